@@ -1,0 +1,272 @@
+// pl_api.cu -- extern "C" entry points of libpl_lattice.so (see include/pl_lattice.h).
+#include <stdarg.h>
+#include <string.h>
+
+#include <new>
+
+#include "pl_common.cuh"
+
+namespace pl {
+
+unsigned long long g_launches = 0;
+static thread_local char t_last_error[512] = "";
+
+void set_last_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_last_error, sizeof(t_last_error), fmt, ap);
+  va_end(ap);
+}
+
+// Stream-ordered allocations from the device's default memory pool; the pool
+// keeps freed blocks (release threshold = max) so repeated builds do not go
+// back to the driver.
+static bool g_pool_ready[64] = {false};
+
+static int ensure_pool(int dev) {
+  if (dev >= 0 && dev < 64 && !g_pool_ready[dev]) {
+    cudaMemPool_t pool;
+    PL_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    uint64_t thr = UINT64_MAX;
+    PL_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    g_pool_ready[dev] = true;
+  }
+  return PL_OK;
+}
+
+int dev_alloc(void** p, size_t bytes, cudaStream_t st) {
+  *p = nullptr;
+  if (bytes == 0) bytes = 16;
+  PL_CUDA(cudaMallocAsync(p, bytes, st));
+  return PL_OK;
+}
+
+void dev_free(void* p, cudaStream_t st) {
+  if (p) cudaFreeAsync(p, st);
+}
+
+static void lattice_release(Lattice* L, cudaStream_t st) {
+  dev_free(L->vid, st);
+  dev_free(L->bary, st);
+  dev_free(L->greedy, st);
+  dev_free(L->rank, st);
+  dev_free(L->vkeys, st);
+  dev_free(L->nbr, st);
+  dev_free(L->val[0], st);
+  dev_free(L->val[1], st);
+  delete L;
+}
+
+static int check_device() {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    set_last_error("no CUDA device: %s", cudaGetErrorString(e));
+    return PL_ERR_NODEVICE;
+  }
+  static int checked[64] = {0};
+  if (dev < 64 && !checked[dev]) {
+    int major = 0;
+    PL_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (major != 10) {
+      set_last_error("device %d is sm_%dx; this library is built for sm_100a only", dev, major);
+      return PL_ERR_NODEVICE;
+    }
+    checked[dev] = 1;
+  }
+  return ensure_pool(dev);
+}
+
+// neighbour table as the tests want it: int32 [d+1][M][2], -1 = absent
+__global__ void __launch_bounds__(256)
+export_nbr_kernel(const int2* __restrict__ nbr, int64_t total, int M, int32_t* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int2 v = nbr[i];
+    out[2 * i + 0] = v.x >= M ? -1 : v.x;
+    out[2 * i + 1] = v.y >= M ? -1 : v.y;
+  }
+}
+
+static int lattice_export(const Lattice* L, int what, void* dst, cudaStream_t st) {
+  const size_t E = (size_t)L->n * (L->d + 1);
+  const void* src = nullptr;
+  size_t bytes = 0;
+  switch (what) {
+    case PL_EXPORT_GREEDY: src = L->greedy; bytes = sizeof(int16_t) * E; break;
+    case PL_EXPORT_RANK: src = L->rank; bytes = sizeof(int8_t) * E; break;
+    case PL_EXPORT_BARY: src = L->bary; bytes = sizeof(float) * E; break;
+    case PL_EXPORT_VERTEX: src = L->vid; bytes = sizeof(int32_t) * E; break;
+    case PL_EXPORT_KEYS: src = L->vkeys; bytes = sizeof(int16_t) * (size_t)L->M * L->d; break;
+    case PL_EXPORT_NEIGHBOURS: {
+      const int64_t total = L->M * (L->d + 1);
+      PL_LAUNCH(export_nbr_kernel, grid_for((uint64_t)total, 256, 8), 256, 0, st, L->nbr, total,
+                (int)L->M, (int32_t*)dst);
+      return PL_OK;
+    }
+    default:
+      set_last_error("pl_lattice_export: unknown artefact %d", what);
+      return PL_ERR_INVALID;
+  }
+  PL_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st));
+  return PL_OK;
+}
+
+}  // namespace pl
+
+using pl::Lattice;
+
+extern "C" {
+
+int pl_lattice_create(const float* ref_dev, int64_t n, int d, uint32_t flags, void* stream,
+                      pl_lattice** out) {
+  if (out == nullptr) return PL_ERR_INVALID;
+  *out = nullptr;
+  if (ref_dev == nullptr || n <= 0 || d < 1 || d > PL_MAX_D) {
+    pl::set_last_error("pl_lattice_create: bad arguments (n=%lld, d=%d)", (long long)n, d);
+    return PL_ERR_INVALID;
+  }
+  if (flags & PL_BUILD_REF_GROW_QUIRK) {
+    pl::set_last_error("PL_BUILD_REF_GROW_QUIRK is not implemented yet");
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  cudaStream_t st = (cudaStream_t)stream;
+  Lattice* L = new (std::nothrow) Lattice();
+  if (!L) return PL_ERR_INVALID;
+  L->n = n;
+  L->d = d;
+  L->flags = flags;
+  cudaGetDevice(&L->device);
+  int r = pl::lattice_build(L, ref_dev, st);
+  if (r != PL_OK) {
+    pl::lattice_release(L, st);
+    return r;
+  }
+  *out = reinterpret_cast<pl_lattice*>(L);
+  return PL_OK;
+}
+
+void pl_lattice_destroy(pl_lattice* lat) {
+  if (lat) pl::lattice_release(reinterpret_cast<Lattice*>(lat), (cudaStream_t)0);
+}
+
+int64_t pl_lattice_num_points(const pl_lattice* lat) { return reinterpret_cast<const Lattice*>(lat)->n; }
+int pl_lattice_dim(const pl_lattice* lat) { return reinterpret_cast<const Lattice*>(lat)->d; }
+int64_t pl_lattice_num_vertices(const pl_lattice* lat) { return reinterpret_cast<const Lattice*>(lat)->M; }
+int64_t pl_lattice_device_bytes(const pl_lattice* lat) {
+  const Lattice* L = reinterpret_cast<const Lattice*>(lat);
+  return L->bytes + 2 * (int64_t)sizeof(float) * L->ws_floats;
+}
+
+int pl_lattice_apply(pl_lattice* lat, const float* src_dev, int64_t src_stride, float* dst_dev,
+                     int64_t dst_stride, int C, const float* sub_dev, int64_t sub_stride,
+                     const float* add_dev, int64_t add_stride, uint32_t flags, void* stream) {
+  if (lat == nullptr) return PL_ERR_INVALID;
+  return pl::lattice_apply(reinterpret_cast<Lattice*>(lat), src_dev, src_stride, dst_dev,
+                           dst_stride, C, sub_dev, sub_stride, add_dev, add_stride, flags,
+                           (cudaStream_t)stream);
+}
+
+int pl_filter(const float* src_dev, const float* ref_dev, float* dst_dev, int64_t n, int C, int d,
+              void* stream) {
+  pl_lattice* lat = nullptr;
+  PL_TRY(pl_lattice_create(ref_dev, n, d, PL_BUILD_DEFAULT, stream, &lat));
+  int r = pl_lattice_apply(lat, src_dev, C, dst_dev, C, C, nullptr, 0, nullptr, 0,
+                           PL_APPLY_DEFAULT, stream);
+  pl::lattice_release(reinterpret_cast<Lattice*>(lat), (cudaStream_t)stream);
+  return r;
+}
+
+int pl_filter_host(const float* src_host, const float* ref_host, float* dst_host, int64_t n, int C,
+                   int d, void* stream) {
+  if (src_host == nullptr || ref_host == nullptr || dst_host == nullptr || n <= 0 || C <= 0) {
+    pl::set_last_error("pl_filter_host: bad arguments");
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  cudaStream_t st = (cudaStream_t)stream;
+  float *src = nullptr, *ref = nullptr, *dst = nullptr;
+  const size_t sb = sizeof(float) * (size_t)n * C, rb = sizeof(float) * (size_t)n * d;
+  PL_TRY(pl::dev_alloc((void**)&src, sb, st));
+  PL_TRY(pl::dev_alloc((void**)&ref, rb, st));
+  PL_TRY(pl::dev_alloc((void**)&dst, sb, st));
+  int r = PL_OK;
+  cudaError_t e = cudaMemcpyAsync(ref, ref_host, rb, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(src, src_host, sb, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) {
+    r = pl_filter(src, ref, dst, n, C, d, stream);
+    if (r == PL_OK) e = cudaMemcpyAsync(dst_host, dst, sb, cudaMemcpyDeviceToHost, st);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  pl::dev_free(src, st);
+  pl::dev_free(ref, st);
+  pl::dev_free(dst, st);
+  if (e != cudaSuccess) {
+    pl::set_last_error("pl_filter_host: %s", cudaGetErrorString(e));
+    return PL_ERR_CUDA;
+  }
+  return r;
+}
+
+int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
+                      int64_t n, int L, float scale, void* stream) {
+  return pl::softmax_compat(e_dev, muT_dev, p_dev, q_out_dev, n, L, scale, (cudaStream_t)stream);
+}
+
+int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, float* e_out_dev,
+                 float* work_dev, int L, int niters, float scale, uint32_t flags, void* stream) {
+  if (lat == nullptr || e0_dev == nullptr || muT_dev == nullptr || e_out_dev == nullptr ||
+      work_dev == nullptr || L <= 0 || niters < 0 || e_out_dev == e0_dev) {
+    pl::set_last_error("pl_meanfield: bad arguments");
+    return PL_ERR_INVALID;
+  }
+  Lattice* Lt = reinterpret_cast<Lattice*>(lat);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t n = Lt->n;
+  if (niters == 0) {
+    PL_CUDA(cudaMemcpyAsync(e_out_dev, e0_dev, sizeof(float) * (size_t)n * L,
+                            cudaMemcpyDeviceToDevice, st));
+    return PL_OK;
+  }
+  for (int it = 0; it < niters; it++) {
+    // P = scale * Mu softmax(-E)          crf_module.py:99-100,102 with :71-75
+    PL_TRY(pl::softmax_compat(it == 0 ? e0_dev : e_out_dev, muT_dev, work_dev, nullptr, n, L,
+                              scale, st));
+    // E = E0 + (filter(P) - P)            crf_module.py:101 with gaussian_matrix.py:350-352
+    PL_TRY(pl::lattice_apply(Lt, work_dev, L, e_out_dev, L, L, work_dev, L, e0_dev, L, flags, st));
+  }
+  return PL_OK;
+}
+
+int pl_nchw_to_nlc(const float* src_dev, float* dst_dev, int64_t batch, int C, int64_t n,
+                   float alpha, void* stream) {
+  return pl::nchw_to_nlc(src_dev, dst_dev, batch, C, n, alpha, (cudaStream_t)stream);
+}
+int pl_nlc_to_nchw(const float* src_dev, float* dst_dev, int64_t batch, int C, int64_t n,
+                   float alpha, void* stream) {
+  return pl::nlc_to_nchw(src_dev, dst_dev, batch, C, n, alpha, (cudaStream_t)stream);
+}
+
+int pl_lattice_export(const pl_lattice* lat, int what, void* dst_dev, void* stream) {
+  if (lat == nullptr || dst_dev == nullptr) return PL_ERR_INVALID;
+  return pl::lattice_export(reinterpret_cast<const Lattice*>(lat), what, dst_dev,
+                            (cudaStream_t)stream);
+}
+
+uint64_t pl_launch_count(void) { return pl::g_launches; }
+int pl_version(void) { return PL_VERSION; }
+
+const char* pl_error_string(int code) {
+  switch (code) {
+    case PL_OK: return "ok";
+    case PL_ERR_INVALID: return "invalid argument";
+    case PL_ERR_CUDA: return "CUDA runtime error";
+    case PL_ERR_OVERFLOW: return "lattice hash table overflow";
+    case PL_ERR_NODEVICE: return "no sm_100 CUDA device";
+    default: return "unknown error";
+  }
+}
+const char* pl_last_error(void) { return pl::t_last_error; }
+
+}  // extern "C"

@@ -1,0 +1,90 @@
+// pl_common.cuh -- shared declarations for libpl_lattice (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/pl_lattice.h"
+
+#define PL_SM_COUNT 148  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+namespace pl {
+
+// ---- error plumbing --------------------------------------------------------
+void set_last_error(const char* fmt, ...);
+extern unsigned long long g_launches;  // kernels launched by this library
+
+#define PL_CUDA(expr)                                                                   \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      pl::set_last_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,                  \
+                         cudaGetErrorString(_e));                                       \
+      return PL_ERR_CUDA;                                                               \
+    }                                                                                   \
+  } while (0)
+
+#define PL_TRY(expr)              \
+  do {                            \
+    int _r = (expr);              \
+    if (_r != PL_OK) return _r;   \
+  } while (0)
+
+// Every kernel launch goes through this so pl_launch_count() is honest.
+#define PL_LAUNCH(kernel, grid, block, smem, stream, ...)          \
+  do {                                                             \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);    \
+    pl::g_launches++;                                              \
+    PL_CUDA(cudaGetLastError());                                   \
+  } while (0)
+
+static inline unsigned int ceil_div_u(uint64_t a, uint64_t b) { return (unsigned int)((a + b - 1) / b); }
+
+// Grid for a grid-stride kernel: enough CTAs for `items` but capped at a
+// multiple of the SM count (waves of 148 x ctas_per_sm).
+static inline unsigned int grid_for(uint64_t items, unsigned int block, unsigned int ctas_per_sm) {
+  uint64_t need = (items + block - 1) / block;
+  uint64_t cap = (uint64_t)PL_SM_COUNT * ctas_per_sm;
+  if (need < 1) need = 1;
+  return (unsigned int)(need < cap ? need : cap);
+}
+
+// ---- the lattice handle ----------------------------------------------------
+struct Lattice {
+  int64_t n = 0;       // points
+  int d = 0;           // feature dims
+  int64_t M = 0;       // vertices
+  uint32_t flags = 0;
+  int device = 0;
+  // persistent device arrays
+  int32_t* vid = nullptr;    // [n][d+1] vertex id per (point, remainder)
+  float* bary = nullptr;     // [n][d+1] barycentric weight per (point, remainder)
+  int16_t* greedy = nullptr; // [n][d+1]
+  int8_t* rank = nullptr;    // [n][d+1]
+  int16_t* vkeys = nullptr;  // [M][d]
+  int2* nbr = nullptr;       // [d+1][M] {minus, plus} neighbour ids; M = absent (zero row)
+  // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats
+  float* val[2] = {nullptr, nullptr};
+  int64_t ws_floats = 0;     // floats per buffer
+  int64_t bytes = 0;         // persistent device bytes
+};
+
+// build (pl_build.cu)
+int lattice_build(Lattice* L, const float* ref, cudaStream_t st);
+// value path (pl_filter.cu)
+int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,
+                  int C, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
+                  uint32_t flags, cudaStream_t st);
+// mean field (pl_meanfield.cu)
+int softmax_compat(const float* e, const float* muT, float* p, float* q_out, int64_t n, int L,
+                   float scale, cudaStream_t st);
+int nchw_to_nlc(const float* src, float* dst, int64_t batch, int C, int64_t n, float alpha,
+                cudaStream_t st);
+int nlc_to_nchw(const float* src, float* dst, int64_t batch, int C, int64_t n, float alpha,
+                cudaStream_t st);
+
+// stream-ordered allocation helpers (pl_api.cu)
+int dev_alloc(void** p, size_t bytes, cudaStream_t st);
+void dev_free(void* p, cudaStream_t st);
+
+}  // namespace pl

@@ -1,0 +1,282 @@
+// pl_filter.cu -- splat / blur / slice over a cached lattice (sm_100a).
+//
+// Value layout in HBM: pixel-major src/dst [n][C] (the reference's own layout,
+// permutohedral.h:212-232) and vertex-major lattice values [M+1][Cc], where
+// row M is a permanent zero row that absent blur neighbours point at
+// (the reference's `zero` vector, permutohedral.h:494-495,518,522).  Channels
+// are the contiguous dimension everywhere, so one pixel's / vertex's channel
+// vector is a run of float4s: scatter (splat) issues vector reductions
+// (red.global.add.v4.f32 -> REDG.E.ADD.F32x4), gathers (blur, slice) issue
+// 128-bit loads.
+//
+// Very wide value matrices (the backward pass filters 2L(1+d) channels,
+// crf/gaussian_matrix.py:450-458) are processed in channel chunks so the two
+// ping-pong lattice buffers stay bounded; the lattice itself is reused.
+#include <math.h>
+
+#include "pl_common.cuh"
+
+namespace pl {
+
+namespace {
+
+// ---- small vector helpers ---------------------------------------------------
+template <int VEC>
+struct Vec;
+template <>
+struct Vec<4> {
+  float4 v;
+  __device__ __forceinline__ static Vec load(const float* p) {
+    Vec r;
+    r.v = *reinterpret_cast<const float4*>(p);
+    return r;
+  }
+  __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = v; }
+  __device__ __forceinline__ static Vec zero() {
+    Vec r;
+    r.v = make_float4(0.f, 0.f, 0.f, 0.f);
+    return r;
+  }
+};
+template <>
+struct Vec<1> {
+  float v;
+  __device__ __forceinline__ static Vec load(const float* p) {
+    Vec r;
+    r.v = *p;
+    return r;
+  }
+  __device__ __forceinline__ void store(float* p) const { *p = v; }
+  __device__ __forceinline__ static Vec zero() {
+    Vec r;
+    r.v = 0.f;
+    return r;
+  }
+};
+
+__device__ __forceinline__ void red_add(float* addr, const Vec<4>& x) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(x.v.x),
+               "f"(x.v.y), "f"(x.v.z), "f"(x.v.w)
+               : "memory");
+}
+__device__ __forceinline__ void red_add(float* addr, const Vec<1>& x) { atomicAdd(addr, x.v); }
+
+template <typename F>
+__device__ __forceinline__ Vec<4> map2(const Vec<4>& a, const Vec<4>& b, F f) {
+  Vec<4> r;
+  r.v.x = f(a.v.x, b.v.x);
+  r.v.y = f(a.v.y, b.v.y);
+  r.v.z = f(a.v.z, b.v.z);
+  r.v.w = f(a.v.w, b.v.w);
+  return r;
+}
+template <typename F>
+__device__ __forceinline__ Vec<1> map2(const Vec<1>& a, const Vec<1>& b, F f) {
+  Vec<1> r;
+  r.v = f(a.v, b.v);
+  return r;
+}
+
+// ---------------------------------------------------------------------------
+// splat                                              permutohedral.h:452-455
+//   val[vid[p][r]][c] += bary[p][r] * src[p][c]
+// One thread per (pixel, channel vector); the d+1 (vertex, weight) pairs of a
+// pixel are re-read by the threads sharing it (L1 broadcast).
+// ---------------------------------------------------------------------------
+template <int VEC, typename Idx>
+__global__ void __launch_bounds__(256)
+splat_kernel(const float* __restrict__ src, int64_t src_stride, int Cc,
+             const int32_t* __restrict__ vid, const float* __restrict__ bary, int D1, Idx n,
+             float* __restrict__ val) {
+  const Idx V = (Idx)(Cc / VEC);
+  const Idx total = n * V;
+  for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (Idx)gridDim.x * blockDim.x) {
+    const Idx p = t / V;
+    const int c = (int)(t - p * V) * VEC;
+    const Vec<VEC> s = Vec<VEC>::load(src + (int64_t)p * src_stride + c);
+    const int32_t* pv = vid + (int64_t)p * D1;
+    const float* pw = bary + (int64_t)p * D1;
+    for (int r = 0; r < D1; r++) {
+      const float w = pw[r];
+      Vec<VEC> ws;
+      ws.v = s.v;
+      Vec<VEC> wv;
+      wv = map2(ws, ws, [w](float a, float) { return __fmul_rn(w, a); });
+      red_add(val + (int64_t)pv[r] * Cc + c, wv);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// blur, one axis                                     permutohedral.h:502-527
+//   out[v] = 2 * (0.25 in[v-] + 0.5 in[v] + 0.25 in[v+])
+// evaluated as fma(0.5, in[v+], fma(0.5, in[v-], in[v])): the powers of two
+// are exact, so each fma rounds exactly where the reference's adds round.
+// ---------------------------------------------------------------------------
+template <int VEC, typename Idx>
+__global__ void __launch_bounds__(256)
+blur_kernel(const float* __restrict__ in, float* __restrict__ out, const int2* __restrict__ nbr_j,
+            Idx M, int Cc) {
+  const Idx V = (Idx)(Cc / VEC);
+  const Idx total = M * V;
+  for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (Idx)gridDim.x * blockDim.x) {
+    const Idx v = t / V;
+    const int c = (int)(t - v * V) * VEC;
+    const int2 nb = nbr_j[v];
+    const Vec<VEC> o = Vec<VEC>::load(in + (int64_t)v * Cc + c);
+    const Vec<VEC> a = Vec<VEC>::load(in + (int64_t)nb.x * Cc + c);
+    const Vec<VEC> b = Vec<VEC>::load(in + (int64_t)nb.y * Cc + c);
+    Vec<VEC> r = map2(a, o, [](float x, float y) { return __fmaf_rn(0.5f, x, y); });
+    r = map2(b, r, [](float x, float y) { return __fmaf_rn(0.5f, x, y); });
+    r.store(out + (int64_t)v * Cc + c);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// slice (+ fused epilogue)                           permutohedral.h:473-483
+//   dst[p][c] = sum_r bary[p][r] * val[vid[p][r]][c] / (1 + 2^-d)  - sub + add
+// EXACT: per-term multiply, divide, add, as the reference spells it.
+// otherwise the constant is folded into the weight and accumulated with FMA.
+// ---------------------------------------------------------------------------
+template <int VEC, bool EXACT, typename Idx>
+__global__ void __launch_bounds__(256)
+slice_kernel(const float* __restrict__ val, int Cc, const int32_t* __restrict__ vid,
+             const float* __restrict__ bary, int D1, Idx n, float denom, float* dst,
+             int64_t dst_stride, const float* sub, int64_t sub_stride, const float* add,
+             int64_t add_stride) {
+  const Idx V = (Idx)(Cc / VEC);
+  const Idx total = n * V;
+  const float inv = 1.0f / denom;
+  for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (Idx)gridDim.x * blockDim.x) {
+    const Idx p = t / V;
+    const int c = (int)(t - p * V) * VEC;
+    const int32_t* pv = vid + (int64_t)p * D1;
+    const float* pw = bary + (int64_t)p * D1;
+    Vec<VEC> acc = Vec<VEC>::zero();
+    for (int r = 0; r < D1; r++) {
+      const float w = pw[r];
+      const Vec<VEC> x = Vec<VEC>::load(val + (int64_t)pv[r] * Cc + c);
+      if (EXACT) {
+        acc = map2(acc, x, [w, denom](float a, float b) {
+          return __fadd_rn(a, __fdiv_rn(__fmul_rn(w, b), denom));
+        });
+      } else {
+        const float wi = w * inv;
+        acc = map2(acc, x, [wi](float a, float b) { return __fmaf_rn(wi, b, a); });
+      }
+    }
+    // E = E0 + (filtered - src), crf_module.py:101 with gaussian_matrix.py:352
+    if (sub != nullptr) {
+      const Vec<VEC> s = Vec<VEC>::load(sub + (int64_t)p * sub_stride + c);
+      acc = map2(acc, s, [](float a, float b) { return __fsub_rn(a, b); });
+    }
+    if (add != nullptr) {
+      const Vec<VEC> s = Vec<VEC>::load(add + (int64_t)p * add_stride + c);
+      acc = map2(acc, s, [](float a, float b) { return __fadd_rn(b, a); });
+    }
+    acc.store(dst + (int64_t)p * dst_stride + c);
+  }
+}
+
+bool aligned16(const void* p) { return ((uintptr_t)p & 15u) == 0; }
+
+template <int VEC, typename Idx>
+int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,
+                int Cc, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
+                uint32_t flags, cudaStream_t st) {
+  const int D1 = L->d + 1;
+  const int64_t M = L->M, n = L->n;
+  const size_t row = sizeof(float) * (size_t)Cc;
+  float* cur = L->val[0];
+  float* nxt = L->val[1];
+  // zero the accumulation buffer (incl. row M) and the other buffer's row M
+  PL_CUDA(cudaMemsetAsync(cur, 0, row * (size_t)(M + 1), st));
+  PL_CUDA(cudaMemsetAsync(nxt + (size_t)M * Cc, 0, row, st));
+
+  const uint64_t pix_items = (uint64_t)n * (uint64_t)(Cc / VEC);
+  const uint64_t vtx_items = (uint64_t)M * (uint64_t)(Cc / VEC);
+  PL_LAUNCH((splat_kernel<VEC, Idx>), grid_for(pix_items, 256, 8), 256, 0, st, src, src_stride, Cc,
+            L->vid, L->bary, D1, (Idx)n, cur);
+  for (int j = 0; j < D1; j++) {
+    PL_LAUNCH((blur_kernel<VEC, Idx>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
+              L->nbr + (size_t)j * M, (Idx)M, Cc);
+    float* t = cur;
+    cur = nxt;
+    nxt = t;
+  }
+  const float denom = 1 + powf(2, -L->d);  // permutohedral.h:480
+  if (flags & PL_APPLY_EXACT_SLICE) {
+    PL_LAUNCH((slice_kernel<VEC, true, Idx>), grid_for(pix_items, 256, 8), 256, 0, st, cur, Cc,
+              L->vid, L->bary, D1, (Idx)n, denom, dst, dst_stride, sub, sub_stride, add,
+              add_stride);
+  } else {
+    PL_LAUNCH((slice_kernel<VEC, false, Idx>), grid_for(pix_items, 256, 8), 256, 0, st, cur, Cc,
+              L->vid, L->bary, D1, (Idx)n, denom, dst, dst_stride, sub, sub_stride, add,
+              add_stride);
+  }
+  return PL_OK;
+}
+
+}  // namespace
+
+int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,
+                  int C, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
+                  uint32_t flags, cudaStream_t st) {
+  if (C <= 0 || src == nullptr || dst == nullptr || src_stride < C || dst_stride < C ||
+      (sub != nullptr && sub_stride < C) || (add != nullptr && add_stride < C)) {
+    set_last_error("pl_lattice_apply: bad arguments (C=%d)", C);
+    return PL_ERR_INVALID;
+  }
+  const bool vec4 = (C % 4 == 0) && (src_stride % 4 == 0) && (dst_stride % 4 == 0) &&
+                    aligned16(src) && aligned16(dst) &&
+                    (sub == nullptr || (sub_stride % 4 == 0 && aligned16(sub))) &&
+                    (add == nullptr || (add_stride % 4 == 0 && aligned16(add)));
+  // channel chunk: both ping-pong buffers together stay under ~4 GiB
+  const int64_t rows = L->M + 1;
+  int64_t max_c = (int64_t)((2ull << 30) / (sizeof(float) * (uint64_t)rows));
+  if (max_c < 4) max_c = 4;
+  if (vec4) max_c &= ~(int64_t)3;
+  const int chunk = (int)(C < max_c ? C : max_c);
+
+  const int64_t need = rows * chunk;
+  if (L->ws_floats < need) {
+    for (int k = 0; k < 2; k++) {
+      if (L->val[k]) dev_free(L->val[k], st);
+      L->val[k] = nullptr;
+    }
+    L->ws_floats = 0;
+    PL_TRY(dev_alloc((void**)&L->val[0], sizeof(float) * (size_t)need, st));
+    PL_TRY(dev_alloc((void**)&L->val[1], sizeof(float) * (size_t)need, st));
+    L->ws_floats = need;
+  }
+
+  for (int c0 = 0; c0 < C; c0 += chunk) {
+    const int Cc = (C - c0) < chunk ? (C - c0) : chunk;
+    const uint64_t items = (uint64_t)(L->n > L->M ? L->n : L->M) * (uint64_t)Cc;
+    const bool small = items < 0x7fffffffull;
+    const float* s = src + c0;
+    float* o = dst + c0;
+    const float* sb = sub ? sub + c0 : nullptr;
+    const float* ad = add ? add + c0 : nullptr;
+    int r;
+    if (vec4 && small)
+      r = apply_chunk<4, uint32_t>(L, s, src_stride, o, dst_stride, Cc, sb, sub_stride, ad,
+                                   add_stride, flags, st);
+    else if (vec4)
+      r = apply_chunk<4, uint64_t>(L, s, src_stride, o, dst_stride, Cc, sb, sub_stride, ad,
+                                   add_stride, flags, st);
+    else if (small)
+      r = apply_chunk<1, uint32_t>(L, s, src_stride, o, dst_stride, Cc, sb, sub_stride, ad,
+                                   add_stride, flags, st);
+    else
+      r = apply_chunk<1, uint64_t>(L, s, src_stride, o, dst_stride, Cc, sb, sub_stride, ad,
+                                   add_stride, flags, st);
+    PL_TRY(r);
+  }
+  return PL_OK;
+}
+
+}  // namespace pl

@@ -1,0 +1,183 @@
+"""Drop-in for the reference's native module ``lattice`` (crf/lattice/lite/lattice.cpp:6-16).
+
+The reference JIT-builds a pybind module exporting one function,
+``filter(src[n,C], ref[n,d]) -> [n,C]`` (crf/gaussian_matrix.py:15-16 binds it
+as ``latticefilter``).  This module exports the same ``filter`` on top of the
+C ABI (include/pl_lattice.h) plus the handle the reference lacks:
+``PermutohedralLattice(ref)`` builds the lattice once, ``.filter(src)`` applies
+it any number of times (every mean-field iteration and the backward pass reuse
+one lattice; the reference rebuilds it per call, permutohedral.h:208,236-238).
+
+Tensors: fp32.  CUDA tensors stay on the device.  CPU tensors (what the
+reference op takes) are copied to the current CUDA device, filtered there and
+copied back -- there is no CPU implementation in this package.
+"""
+import ctypes as C
+
+import torch
+
+from . import _native as N
+
+
+class PermutohedralLattice:
+    """Cached lattice for one feature matrix ``ref[n, d]`` (CUDA, fp32).
+
+    Mirrors the reference class of the same name (permutohedral.h:186-578):
+    construction = its constructor + the position-dependent half of splat()
+    for all points; ``filter`` = splat values -> blur -> slice.
+    """
+
+    def __init__(self, ref, ref_grow_quirk=False):
+        N.require_cuda_f32(ref, "ref", 2)
+        ref = ref.contiguous()
+        self.device = ref.device
+        self.n, self.d = int(ref.shape[0]), int(ref.shape[1])
+        self._h = C.c_void_p()
+        flags = N.PL_BUILD_REF_GROW_QUIRK if ref_grow_quirk else N.PL_BUILD_DEFAULT
+        with torch.cuda.device(self.device):
+            N.check(N.lib().pl_lattice_create(C.c_void_p(ref.data_ptr()), self.n, self.d, flags,
+                                              N.stream_ptr(self.device), C.byref(self._h)))
+        self.num_vertices = int(N.lib().pl_lattice_num_vertices(self._h))
+
+    # -- value path ---------------------------------------------------------
+    def filter(self, src, sub=None, add=None, exact_slice=False, out=None):
+        """``filter(src) - sub + add`` for ``src[n, C]`` (row stride may exceed C).
+
+        ``sub=src`` is the adjacency ``W(x) = K x - x`` (gaussian_matrix.py:302,352);
+        ``add=E0`` fuses the mean-field update (crf_module.py:101).
+        """
+        self._check_rows(src, "src")
+        src = _rowmajor(src)
+        c = int(src.shape[1])
+        if out is None:
+            out = torch.empty((self.n, c), dtype=torch.float32, device=self.device)
+        else:
+            self._check_rows(out, "out")
+            if out.shape[1] != c or out.stride(1) != 1:
+                raise ValueError("out must be [n, C] with unit channel stride")
+        ptrs, strides = [], []
+        for name, t in (("sub", sub), ("add", add)):
+            if t is None:
+                ptrs.append(C.c_void_p(0))
+                strides.append(0)
+            else:
+                self._check_rows(t, name)
+                if t.shape[1] != c:
+                    raise ValueError(f"{name} must have {c} channels")
+                t = _rowmajor(t)
+                ptrs.append(C.c_void_p(t.data_ptr()))
+                strides.append(t.stride(0))
+        flags = N.PL_APPLY_EXACT_SLICE if exact_slice else N.PL_APPLY_DEFAULT
+        with torch.cuda.device(self.device):
+            N.check(N.lib().pl_lattice_apply(
+                self._h, C.c_void_p(src.data_ptr()), src.stride(0), C.c_void_p(out.data_ptr()),
+                out.stride(0), c, ptrs[0], strides[0], ptrs[1], strides[1], flags,
+                N.stream_ptr(self.device)))
+        return out
+
+    __call__ = filter
+
+    def mean_field(self, e0, mu, niters, scale=1.0, exact_slice=False):
+        """Pixel-major CRFasRNN inference loop (crf_module.py:97-103).
+
+        ``e0[n, L]`` unary energies, ``mu[L, L]`` compatibility matrix
+        (``Mu[l][k]``, crf_module.py:74); returns E of the last iteration.
+        """
+        self._check_rows(e0, "e0")
+        e0 = e0.contiguous()
+        L = int(e0.shape[1])
+        N.require_cuda_f32(mu, "mu", 2)
+        if tuple(mu.shape) != (L, L):
+            raise ValueError(f"mu must be [{L}, {L}]")
+        mu_t = mu.t().contiguous()
+        out = torch.empty_like(e0)
+        work = torch.empty_like(e0)
+        flags = N.PL_APPLY_EXACT_SLICE if exact_slice else N.PL_APPLY_DEFAULT
+        with torch.cuda.device(self.device):
+            N.check(N.lib().pl_meanfield(
+                self._h, C.c_void_p(e0.data_ptr()), C.c_void_p(mu_t.data_ptr()),
+                C.c_void_p(out.data_ptr()), C.c_void_p(work.data_ptr()), L, int(niters),
+                float(scale), flags, N.stream_ptr(self.device)))
+        return out
+
+    # -- inspection (parity tests) -------------------------------------------
+    def export(self):
+        """Integer / float artefacts as torch tensors (see PL_EXPORT_* in pl_lattice.h)."""
+        n, d, M = self.n, self.d, self.num_vertices
+        dev = self.device
+        out = {
+            "greedy": (N.PL_EXPORT_GREEDY, torch.empty((n, d + 1), dtype=torch.int16, device=dev)),
+            "rank": (N.PL_EXPORT_RANK, torch.empty((n, d + 1), dtype=torch.int8, device=dev)),
+            "bary": (N.PL_EXPORT_BARY, torch.empty((n, d + 1), dtype=torch.float32, device=dev)),
+            "vid": (N.PL_EXPORT_VERTEX, torch.empty((n, d + 1), dtype=torch.int32, device=dev)),
+            "keys": (N.PL_EXPORT_KEYS, torch.empty((M, d), dtype=torch.int16, device=dev)),
+            "nbr": (N.PL_EXPORT_NEIGHBOURS,
+                    torch.empty((d + 1, M, 2), dtype=torch.int32, device=dev)),
+        }
+        with torch.cuda.device(dev):
+            for what, t in out.values():
+                N.check(N.lib().pl_lattice_export(self._h, what, C.c_void_p(t.data_ptr()),
+                                                  N.stream_ptr(dev)))
+        return {k: t for k, (_, t) in out.items()}
+
+    @property
+    def device_bytes(self):
+        return int(N.lib().pl_lattice_device_bytes(self._h))
+
+    def _check_rows(self, t, name):
+        N.require_cuda_f32(t, name, 2)
+        if t.device != self.device:
+            raise ValueError(f"{name} is on {t.device}, lattice on {self.device}")
+        if t.shape[0] != self.n:
+            # same message as the reference's assert (gaussian_matrix.py:429-430)
+            raise AssertionError("Incompatible shapes {}, and {}".format(tuple(t.shape),
+                                                                        (self.n, self.d)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            N.lib().pl_lattice_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _rowmajor(t):
+    """[n, C] view with unit channel stride and a 16-byte friendly row stride."""
+    if t.stride(1) != 1 or t.stride(0) < t.shape[1]:
+        t = t.contiguous()
+    return t
+
+
+def filter(src, ref):  # noqa: A001 - the reference's exported name
+    """``lattice.filter(src[n,C], ref[n,d]) -> [n,C]`` (lattice.cpp:6-10).
+
+    Output lives where ``src`` lives.  CPU inputs are staged through the GPU.
+    """
+    if src.dim() != 2 or ref.dim() != 2:
+        raise ValueError("filter expects src[n,C] and ref[n,d]")
+    assert src.shape[0] == ref.shape[0], \
+        "Incompatible shapes {}, and {}".format(tuple(src.shape), tuple(ref.shape))
+    if src.dtype != torch.float32 or ref.dtype != torch.float32:
+        raise TypeError("filter expects float32 tensors (permutohedral.h:19 float_type)")
+    n, c, d = int(src.shape[0]), int(src.shape[1]), int(ref.shape[1])
+    if not src.is_cuda:
+        # the reference's own call shape: host buffers in, host buffer out
+        if not torch.cuda.is_available():
+            raise N.LatticeError("lattice.filter needs a CUDA device (no CPU fallback)")
+        src_c, ref_c = src.contiguous(), ref.cpu().contiguous()
+        out = torch.empty_like(src_c, pin_memory=src_c.is_pinned())
+        N.check(N.lib().pl_filter_host(C.c_void_p(src_c.data_ptr()), C.c_void_p(ref_c.data_ptr()),
+                                       C.c_void_p(out.data_ptr()), n, c, d,
+                                       N.stream_ptr(torch.cuda.current_device())))
+        return out
+    N.require_cuda_f32(ref, "ref", 2)
+    src_c, ref_c = src.contiguous(), ref.contiguous()
+    out = torch.empty_like(src_c)
+    with torch.cuda.device(src.device):
+        N.check(N.lib().pl_filter(C.c_void_p(src_c.data_ptr()), C.c_void_p(ref_c.data_ptr()),
+                                  C.c_void_p(out.data_ptr()), n, c, d, N.stream_ptr(src.device)))
+    return out

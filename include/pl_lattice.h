@@ -1,0 +1,155 @@
+/*
+ * pl_lattice.h -- C ABI of the B200-native permutohedral-lattice filter and
+ * dense-CRF mean-field loop (libpl_lattice.so, built from
+ * depth-estimation_b200/csrc/ for sm_100a).
+ *
+ * This is the drop-in boundary for the reference's one native export,
+ *     at::Tensor filter(at::Tensor src, at::Tensor ref)
+ *         crf/lattice/lite/lattice.cpp:6-16  (pybind module `lattice`,
+ *         JIT-loaded by crf/gaussian_matrix.py:15-16 as `latticefilter`),
+ * whose body is PermutohedralLattice::filter (crf/lattice/lite/permutohedral.h
+ * :199-321): build lattice from ref[n,d] -> splat src[n,C] -> blur -> slice.
+ *
+ * Plain pointers and sizes only; no torch types.  All `*_dev` pointers are
+ * device pointers on the current CUDA device, fp32, row-major; `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream).  Every call is
+ * asynchronous on `stream` unless stated otherwise.  Functions return PL_OK or
+ * a PL_ERR_* code; pl_error_string() / pl_last_error() describe it.  There is
+ * no CPU fallback anywhere in this library.
+ *
+ * The reference rebuilds the lattice inside every filter() call
+ * (permutohedral.h:208,236-238).  Here the lattice is a handle that is built
+ * once per feature matrix and applied many times (every mean-field iteration
+ * and the backward pass reuse it); pl_filter() is the one-shot spelling with
+ * exactly the reference's call shape.
+ */
+#ifndef PL_LATTICE_H
+#define PL_LATTICE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PL_VERSION 1
+
+enum {
+  PL_OK = 0,
+  PL_ERR_INVALID = 1,   /* bad argument (null pointer, n<=0, d out of range, ...) */
+  PL_ERR_CUDA = 2,      /* a CUDA runtime call failed; see pl_last_error() */
+  PL_ERR_OVERFLOW = 3,  /* lattice hash table could not be sized (internal retry exhausted) */
+  PL_ERR_NODEVICE = 4   /* no CUDA device / not an sm_100 device */
+};
+
+#define PL_MAX_D 16 /* feature dimensions supported (reference: char rank, d <= 127) */
+
+typedef struct pl_lattice pl_lattice; /* opaque */
+
+/* ---- lattice handle ------------------------------------------------------- */
+
+/* pl_lattice_create flags */
+#define PL_BUILD_DEFAULT 0u
+/* Reproduce the reference's hash-table growth quirk (permutohedral.h:102-103
+ * with :62: the lookup that triggers a table doubling probes from a slot
+ * computed with the old capacity, which can create one orphan duplicate
+ * vertex per doubling).  Off: one vertex per distinct key (the algorithm as
+ * published).  The two are identical whenever the reference table never grows
+ * (M < 16383). */
+#define PL_BUILD_REF_GROW_QUIRK 1u
+
+/* Builds the lattice for feature vectors ref_dev[n][d] (what the reference's
+ * splat() derives from `position`: permutohedral.h:376-450 minus the value
+ * accumulation, plus the neighbour table blur() looks up at :503-522).
+ * Synchronises `stream` once (the vertex count has to reach the host). */
+int pl_lattice_create(const float* ref_dev, int64_t n, int d, uint32_t flags, void* stream,
+                      pl_lattice** out);
+void pl_lattice_destroy(pl_lattice* lat);
+
+int64_t pl_lattice_num_points(const pl_lattice* lat);   /* n */
+int pl_lattice_dim(const pl_lattice* lat);              /* d */
+int64_t pl_lattice_num_vertices(const pl_lattice* lat); /* M == hashTable.size() (permutohedral.h:45) */
+int64_t pl_lattice_device_bytes(const pl_lattice* lat); /* persistent device memory held */
+
+/* pl_lattice_apply flags */
+#define PL_APPLY_DEFAULT 0u
+/* Evaluate slice exactly as permutohedral.h:480 does (per-term fp32 divide by
+ * 1+2^-d, no FMA contraction) instead of folding the constant into the
+ * barycentric weight. */
+#define PL_APPLY_EXACT_SLICE 1u
+
+/* dst[p][c] = filter(src)[p][c] - (sub ? sub[p][c] : 0) + (add ? add[p][c] : 0)
+ *
+ * filter = splat (permutohedral.h:452-455) -> blur (:486-548) -> slice
+ * (:473-483) on the cached lattice; identical to the reference's
+ * filter(src, ref) when sub == add == NULL.  `sub = src` gives the adjacency
+ * form W(x) = filter(x) - x of crf/gaussian_matrix.py:302,352; `add = E0`
+ * fuses the mean-field update E = E0 + W(..) of crf/crf_module.py:101.
+ * src/dst/sub/add are [n][C] with row strides given in floats (>= C);
+ * dst may alias sub or add but not src. */
+int pl_lattice_apply(pl_lattice* lat, const float* src_dev, int64_t src_stride, float* dst_dev,
+                     int64_t dst_stride, int C, const float* sub_dev, int64_t sub_stride,
+                     const float* add_dev, int64_t add_stride, uint32_t flags, void* stream);
+
+/* ---- the reference's call shape ------------------------------------------- */
+
+/* lattice.cpp:6-10  filter(src[n,C], ref[n,d]) -> dst[n,C], device buffers. */
+int pl_filter(const float* src_dev, const float* ref_dev, float* dst_dev, int64_t n, int C, int d,
+              void* stream);
+
+/* Same with HOST buffers (what the reference's CPU op takes and returns):
+ * copies src/ref to the device, filters, copies dst back, synchronises.
+ * Pinned host memory makes the copies asynchronous; pageable works too. */
+int pl_filter_host(const float* src_host, const float* ref_host, float* dst_host, int64_t n, int C,
+                   int d, void* stream);
+
+/* ---- mean-field pieces (crf/crf_module.py:41-53, 66-75, 93-104) ----------- */
+
+/* P[p][l] = scale * sum_k Mu[l][k] * softmax_k(-E[p][.])[k]
+ * i.e. Q = F.softmax(-E, dim=1) followed by charb.forward's 1x1 conv2d with
+ * the L x L compatibility matrix times exp(s) (crf_module.py:71-75), in
+ * pixel-major layout.  muT_dev is Mu transposed, [L(k)][L(l)] row-major.
+ * q_out_dev (optional, may be NULL) receives Q. */
+int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
+                      int64_t n, int L, float scale, void* stream);
+
+/* Whole inference loop of CRFasRNN.forward (crf_module.py:93-104) with
+ * W = lattice adjacency (gaussian_matrix.py:341-352), pixel-major:
+ *   E = E0; repeat niters: P = scale * Mu softmax(-E); E = E0 + filter(P) - P
+ * e0_dev, e_out_dev: [n][L].  Returns E of the last iteration (the module
+ * returns -E).  work_dev: caller-provided scratch of n*L floats. */
+int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, float* e_out_dev,
+                 float* work_dev, int L, int niters, float scale, uint32_t flags, void* stream);
+
+/* Layout helpers for the module surface (NCHW tensors <-> pixel-major):
+ * dst[b][p][c] = alpha * src[b][c][p]   and back. */
+int pl_nchw_to_nlc(const float* src_dev, float* dst_dev, int64_t batch, int C, int64_t n,
+                   float alpha, void* stream);
+int pl_nlc_to_nchw(const float* src_dev, float* dst_dev, int64_t batch, int C, int64_t n,
+                   float alpha, void* stream);
+
+/* ---- inspection (parity tests read the integer artefacts through these) --- */
+
+enum {
+  PL_EXPORT_GREEDY = 0,   /* int16 [n][d+1]  permutohedral.h:398-399,418,428 */
+  PL_EXPORT_RANK = 1,     /* int8  [n][d+1]  permutohedral.h:407-433 */
+  PL_EXPORT_BARY = 2,     /* f32   [n][d+1]  permutohedral.h:436-441 (replay weight :459) */
+  PL_EXPORT_VERTEX = 3,   /* int32 [n][d+1]  replay offset / vd (:458), first-touch numbering */
+  PL_EXPORT_KEYS = 4,     /* int16 [M][d]    hashTable.getKeys() (:48) */
+  PL_EXPORT_NEIGHBOURS = 5/* int32 [d+1][M][2], -1 = absent (:516-522) */
+};
+/* Copies one artefact into dst_dev (device memory, sized as listed). */
+int pl_lattice_export(const pl_lattice* lat, int what, void* dst_dev, void* stream);
+
+/* ---- bookkeeping ---------------------------------------------------------- */
+
+/* Number of kernels this library has launched in this process so far. */
+uint64_t pl_launch_count(void);
+int pl_version(void);
+const char* pl_error_string(int code);
+const char* pl_last_error(void); /* detail of the most recent failure on this thread */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PL_LATTICE_H */
