@@ -47,6 +47,8 @@ _SIGNATURES = {
     "pl_nlc_to_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_float,
                                  C.c_void_p]),
     "pl_lattice_export": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "pl_profile": (None, [C.c_int]),
+    "pl_profile_report": (C.c_int, [C.c_char_p, C.c_int]),
     "pl_launch_count": (C.c_uint64, []),
     "pl_version": (C.c_int, []),
     "pl_error_string": (C.c_char_p, [C.c_int]),
@@ -97,6 +99,21 @@ def require_cuda_f32(t, name, ndim=None):
         raise TypeError(f"{name} must be float32, got {t.dtype}")
     if ndim is not None and t.dim() != ndim:
         raise ValueError(f"{name} must be {ndim}-D, got shape {tuple(t.shape)}")
+
+
+def profile(enable):
+    lib().pl_profile(1 if enable else 0)
+
+
+def profile_report():
+    """{kernel name: (launches, total_ms)} since profiling was switched on; clears."""
+    buf = C.create_string_buffer(1 << 16)
+    lib().pl_profile_report(buf, len(buf))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, cnt, ms = line.split("\t")
+        out[name.strip("()")] = (int(cnt), float(ms))
+    return out
 
 
 def launch_count():

@@ -1,0 +1,179 @@
+"""Mean-field dense CRF -- mirror of crf/crf_module.py on the GPU lattice.
+
+Same public names and signatures as the reference: ``charbonneir``,
+``charbonneir2``, ``compatibility_matrix`` (:32-39), ``mean_field_infer``
+(:41-53), ``potts`` (:55-64), ``charb`` (:66-79), ``CRFasRNN`` (:81-104),
+``ijrgbGuide`` / ``ijGuide`` (:106-123), ``gaussian_weights(_u)`` (:8-20).
+
+``CRFasRNN.W`` is the lattice adjacency ``BatchedAdjacency`` (the reference
+imports it at :5 and it has the same ``W(src_imgs, guide_imgs)`` call shape as
+the guided-filter adjacency wired at :91).  When no gradient is required the
+forward runs the fused pixel-major loop of libpl_lattice (``pl_meanfield``:
+softmax + compatibility in one kernel, E-update fused into slice, one lattice
+per image reused by all iterations); with autograd enabled it runs the same
+composition of differentiable ops as the reference.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import _native as N
+from .gaussian_matrix import BatchedAdjacency, lattice_for, _cached
+
+
+def gaussian_weights(f):
+    """crf_module.py:8-15 (brute-force dense kernel, tiny n only)."""
+    I = torch.eye(f.shape[0]).to(f.device)
+    W = torch.exp(-((f[None, :, :] - f[:, None, :]) ** 2).sum(-1)) - I
+    D = W @ torch.ones(f.shape[0]).to(f.device)
+    D_invsqrt = torch.diag(1 / torch.sqrt(D))
+    return D_invsqrt @ W @ D_invsqrt - I
+
+
+def gaussian_weights_u(f):
+    """crf_module.py:17-20."""
+    I = torch.eye(f.shape[0]).to(f.device)
+    return torch.exp(-((f[None, :, :] - f[:, None, :]) ** 2).sum(-1)) - I
+
+
+def charbonneir(a, b, gamma=.1):
+    return torch.sqrt(gamma ** 2 + (a - b) ** 2) - gamma
+
+
+def charbonneir2(a, b, gamma=3):
+    return torch.sqrt(1 + ((a - b) / gamma) ** 2) - 1
+
+
+def compatibility_matrix(compat, labels):
+    return compat(labels[:, None], labels[None, :])
+
+
+def mean_field_infer(E_0, W, Mu, niters=10):
+    """crf_module.py:41-53: ``E = E_0 + W @ Q @ Mu`` (filter first, then Mu)."""
+    Q = F.softmax(-E_0, dim=1)
+    for i in range(niters):
+        E = E_0 + W @ Q @ Mu
+        Q = F.softmax(-E, dim=1)
+    return Q
+
+
+def potts(num_classes):
+    """crf_module.py:55-64."""
+    layer = nn.Conv2d(num_classes, num_classes, kernel_size=1, bias=False)
+    with torch.no_grad():
+        layer.weight.fill_(1)
+        layer.weight.sub_(torch.eye(num_classes)[..., None, None])
+    return layer
+
+
+class charb(nn.Module):
+    """crf_module.py:66-79."""
+
+    def __init__(self, gamma):
+        super().__init__()
+        self.gamma = nn.Parameter(torch.tensor(gamma))
+        self.s = nn.Parameter(torch.tensor(0.))
+
+    def matrix(self, L, labels=None, device=None):
+        if labels is None:
+            labels = torch.arange(L).float().to(device if device is not None else self.gamma.device)
+        labels = labels.reshape(-1)
+        return charbonneir(labels[None, :], labels[:, None], self.gamma)
+
+    def forward(self, x, labels=None):
+        L = x.shape[1]
+        Mu = self.matrix(L, labels, x.device)
+        return F.conv2d(x, Mu[..., None, None]) * torch.exp(self.s)
+
+    def get_energies_from_scalar(self, x, labels):
+        return charbonneir(labels, x, self.gamma * labels.max()) * torch.exp(self.s)
+
+
+class CRFasRNN(nn.Module):
+    """crf_module.py:81-104 with the lattice pairwise term."""
+
+    def __init__(self, mu_init, niters=5, r=20, eps=1e-5, notrain_mu=False, gaussian=False,
+                 gchannels=1, fused=True):
+        super().__init__()
+        self.Mu = mu_init
+        if notrain_mu:
+            for param in self.Mu.parameters():
+                param.requires_grad = False
+        self.niters = niters
+        # r / eps / gaussian / gchannels parametrise the reference's guided-filter
+        # adjacency (:91); the lattice adjacency has no such knobs.
+        self.W = BatchedAdjacency()
+        self.fused = fused
+
+    def forward(self, refs, logits, confidence=None, labels=None):
+        """Assuming E0 and Refs are shape BxLxHxW and BxCxHxW"""
+        if confidence is None:
+            confidence = 1
+        E0 = -logits * confidence
+        needs_grad = torch.is_grad_enabled() and (
+            E0.requires_grad or refs.requires_grad or
+            any(p.requires_grad for p in self.Mu.parameters()))
+        if self.fused and not needs_grad and isinstance(self.Mu, charb) and self.niters > 0:
+            return self._forward_fused(refs, E0, labels)
+        Mu = (lambda q: self.Mu(q)) if labels is None else (lambda q: self.Mu(q, labels))
+        Q = F.softmax(-E0, dim=1)
+        for i in range(self.niters):
+            E = E0 + self.W(Mu(Q), refs)
+            Q = F.softmax(-E, dim=1)
+        return -E
+
+    def _forward_fused(self, refs, E0, labels):
+        B, L, H, W = E0.shape
+        n, d = H * W, refs.shape[1]
+        dev = E0.device
+        with torch.no_grad():
+            mu = self.Mu.matrix(L, labels, dev).float().contiguous()
+            scale = float(torch.exp(self.Mu.s))
+            flat_refs = _cached(
+                refs, lambda: refs.reshape(B, d, -1).permute(0, 2, 1).contiguous())
+            E0c = E0.float().contiguous()
+            e0_nl = torch.empty((B, n, L), dtype=torch.float32, device=dev)
+            st = N.stream_ptr(dev)
+            with torch.cuda.device(dev):
+                N.check(N.lib().pl_nchw_to_nlc(C.c_void_p(E0c.data_ptr()),
+                                               C.c_void_p(e0_nl.data_ptr()), B, L, n, 1.0, st))
+            e_nl = torch.stack([lattice_for(flat_refs[b]).mean_field(e0_nl[b], mu, self.niters, scale)
+                                for b in range(B)])
+            out = torch.empty_like(E0c)
+            with torch.cuda.device(dev):
+                # the module returns -E (:103)
+                N.check(N.lib().pl_nlc_to_nchw(C.c_void_p(e_nl.data_ptr()),
+                                               C.c_void_p(out.data_ptr()), B, L, n, -1.0, st))
+        return out
+
+
+class ijrgbGuide(nn.Module):
+    """crf_module.py:106-114: guide = cat(ij / s_ij, rgb / s_rgb), ij = mgrid / sqrt(h^2+w^2)."""
+
+    def __init__(self, s_ij=.1, s_rgb=.1, trainable=True):
+        super().__init__()
+        self.s_ij = nn.Parameter(torch.tensor(s_ij)) if trainable else s_ij
+        self.s_rgb = nn.Parameter(torch.tensor(s_rgb)) if trainable else s_rgb
+
+    def forward(self, x):
+        bs, c, h, w = x.shape
+        ij = torch.from_numpy(np.tile(np.mgrid[:h, :w] / np.sqrt(h ** 2 + w ** 2),
+                                      (bs, 1, 1, 1))).float().to(x.device)
+        return torch.cat([ij / self.s_ij, x / self.s_rgb], dim=1)
+
+
+class ijGuide(nn.Module):
+    """crf_module.py:116-123."""
+
+    def __init__(self, s_ij=.1, trainable=True):
+        super().__init__()
+        self.s_ij = nn.Parameter(torch.tensor(s_ij)) if trainable else s_ij
+
+    def forward(self, x):
+        bs, c, h, w = x.shape
+        ij = torch.from_numpy(np.tile(np.mgrid[:h, :w] / np.sqrt(h ** 2 + w ** 2),
+                                      (bs, 1, 1, 1))).float().to(x.device)
+        return ij / self.s_ij

@@ -31,7 +31,7 @@ latticefilter = _lattice.filter  # gaussian_matrix.py:16
 # the entry lives; the key also carries the version counter, so an in-place
 # update of the features (through any view) invalidates it.
 _CACHE = {}
-_CACHE_MAX = 16
+_CACHE_MAX = 128
 
 
 def _key(t):

@@ -3,6 +3,8 @@
 #include <string.h>
 
 #include <new>
+#include <string>
+#include <vector>
 
 #include "pl_common.cuh"
 
@@ -16,6 +18,26 @@ void set_last_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(t_last_error, sizeof(t_last_error), fmt, ap);
   va_end(ap);
+}
+
+// ---- optional per-launch timing (pl_profile / pl_profile_report) -------------
+bool g_prof_on = false;
+struct ProfRec {
+  const char* name;
+  cudaEvent_t a, b;
+};
+static std::vector<ProfRec> g_prof;
+
+void prof_begin(const char* name, cudaStream_t st) {
+  ProfRec r;
+  r.name = name;
+  cudaEventCreate(&r.a);
+  cudaEventCreate(&r.b);
+  cudaEventRecord(r.a, st);
+  g_prof.push_back(r);
+}
+void prof_end(cudaStream_t st) {
+  if (!g_prof.empty()) cudaEventRecord(g_prof.back().b, st);
 }
 
 // Stream-ordered allocations from the device's default memory pool; the pool
@@ -252,6 +274,39 @@ int pl_lattice_export(const pl_lattice* lat, int what, void* dst_dev, void* stre
   if (lat == nullptr || dst_dev == nullptr) return PL_ERR_INVALID;
   return pl::lattice_export(reinterpret_cast<const Lattice*>(lat), what, dst_dev,
                             (cudaStream_t)stream);
+}
+
+void pl_profile(int enable) { pl::g_prof_on = enable != 0; }
+
+int pl_profile_report(char* buf, int cap) {
+  // one line per kernel: "<name>\t<launches>\t<total_ms>"; clears the records
+  struct Agg { std::string name; int count; double ms; };
+  std::vector<Agg> agg;
+  for (auto& r : pl::g_prof) {
+    cudaEventSynchronize(r.b);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+    std::string nm(r.name);
+    size_t i = 0;
+    for (; i < agg.size(); i++) if (agg[i].name == nm) break;
+    if (i == agg.size()) agg.push_back({nm, 0, 0.0});
+    agg[i].count++;
+    agg[i].ms += ms;
+  }
+  pl::g_prof.clear();
+  std::string out;
+  char line[256];
+  for (auto& a : agg) {
+    snprintf(line, sizeof(line), "%s\t%d\t%.6f\n", a.name.c_str(), a.count, a.ms);
+    out += line;
+  }
+  if (buf != nullptr && cap > 0) {
+    strncpy(buf, out.c_str(), (size_t)cap - 1);
+    buf[cap - 1] = 0;
+  }
+  return (int)out.size();
 }
 
 uint64_t pl_launch_count(void) { return pl::g_launches; }

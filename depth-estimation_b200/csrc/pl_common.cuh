@@ -30,10 +30,18 @@ extern unsigned long long g_launches;  // kernels launched by this library
     if (_r != PL_OK) return _r;   \
   } while (0)
 
-// Every kernel launch goes through this so pl_launch_count() is honest.
+// Every kernel launch goes through this so pl_launch_count() is honest.  With
+// pl_profile(1) each launch is additionally bracketed by CUDA events on its
+// own stream (bench.py reads per-kernel durations for the roofline that way).
+void prof_begin(const char* name, cudaStream_t st);
+void prof_end(cudaStream_t st);
+extern bool g_prof_on;
+
 #define PL_LAUNCH(kernel, grid, block, smem, stream, ...)          \
   do {                                                             \
+    if (pl::g_prof_on) pl::prof_begin(#kernel, (stream));          \
     kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);    \
+    if (pl::g_prof_on) pl::prof_end((stream));                     \
     pl::g_launches++;                                              \
     PL_CUDA(cudaGetLastError());                                   \
   } while (0)

@@ -143,6 +143,14 @@ int pl_lattice_export(const pl_lattice* lat, int what, void* dst_dev, void* stre
 
 /* ---- bookkeeping ---------------------------------------------------------- */
 
+/* Per-launch timing for the roofline report: pl_profile(1) brackets every
+ * kernel launch with CUDA events on its stream; pl_profile_report() waits for
+ * them, writes one "<kernel>\t<launches>\t<total_ms>" line per kernel into
+ * buf (NUL-terminated, truncated to cap), clears the records and returns the
+ * untruncated length.  Not for use inside a timed region. */
+void pl_profile(int enable);
+int pl_profile_report(char* buf, int cap);
+
 /* Number of kernels this library has launched in this process so far. */
 uint64_t pl_launch_count(void);
 int pl_version(void);

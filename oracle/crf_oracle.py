@@ -1,0 +1,124 @@
+"""CPU restatement of the reference's Python layer (TEST INFRASTRUCTURE, not product code).
+
+Follows crf/gaussian_matrix.py and crf/crf_module.py line by line in torch-CPU
+fp32 on top of the oracle filter (oracle/lattice_oracle.py), because the
+reference modules cannot be imported as they stand (gaussian_matrix.py:8 needs
+the un-vendored ``guided_filter_pytorch``; :15 JIT-loads a hard-coded path).
+tests/golden/make_golden.py additionally imports the REAL reference modules
+through stubs to pin this file.
+"""
+import numpy as np
+import torch
+import torch.nn.functional as F
+from torch.autograd import Function
+
+from .lattice_oracle import Oracle
+
+_ORACLE = None
+
+
+def set_backend(o):
+    global _ORACLE
+    _ORACLE = o
+
+
+def latticefilter(src, ref):
+    """gaussian_matrix.py:16 ``lattice.filter`` on CPU tensors."""
+    global _ORACLE
+    if _ORACLE is None:
+        _ORACLE = Oracle(faithful=False)
+    out = _ORACLE.filter(src.detach().contiguous().numpy(), ref.detach().contiguous().numpy())
+    return torch.from_numpy(out)
+
+
+class LatticeFilter(Function):
+    """gaussian_matrix.py:423-468 (without the stray print at :467)."""
+
+    @staticmethod
+    def forward(ctx, source, reference):
+        assert source.shape[0] == reference.shape[0]
+        ctx.save_for_backward(source, reference)
+        return latticefilter(source, reference)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        with torch.no_grad():
+            src, ref = ctx.saved_tensors
+            g = grad_output
+            n, L = src.shape[-2:]
+            d = ref.shape[-1]
+            grad_source = grad_reference = None
+            if ctx.needs_input_grad[0] and not ctx.needs_input_grad[1]:
+                grad_source = latticefilter(g, ref)
+            if ctx.needs_input_grad[1]:
+                gf = g[..., None] * ref[..., None, :]
+                sf = src[..., None] * ref[..., None, :]
+                all_ = torch.cat([g, gf.reshape(n, L * d), src, sf.reshape(n, L * d)], dim=-1)
+                filtered_all = latticefilter(all_, ref)
+                wg, wgf, ws, wsf = torch.split(filtered_all, [L, L * d, L, L * d], dim=-1)
+                grad_reference = -2 * (sf * wg[..., None] - src[..., None] * wgf.view(-1, L, d)
+                                       + gf * ws[..., None] - g[..., None] * wsf.view(-1, L, d)).sum(-2)
+                if ctx.needs_input_grad[0]:
+                    grad_source = wg
+        return grad_source, grad_reference
+
+
+def batched_adjacency(src_imgs, guide_imgs):
+    """gaussian_matrix.py:345-352 (BatchedAdjacency.forward), sans mp.Pool."""
+    bs, L, h, w = src_imgs.shape
+    d = guide_imgs.shape[1]
+    flat_srcs = src_imgs.reshape(bs, L, -1).permute(0, 2, 1)
+    flat_refs = guide_imgs.reshape(bs, d, -1).permute(0, 2, 1)
+    filtered = torch.stack([LatticeFilter.apply(s.contiguous(), r.contiguous())
+                            for s, r in zip(flat_srcs, flat_refs)])
+    return filtered.permute(0, 2, 1).reshape(src_imgs.shape) - src_imgs
+
+
+def charbonneir(a, b, gamma=.1):
+    return torch.sqrt(gamma ** 2 + (a - b) ** 2) - gamma  # crf_module.py:32-33
+
+
+def charb_forward(x, gamma, s, labels=None):
+    """crf_module.py:71-75."""
+    L = x.shape[1]
+    if labels is None:
+        labels = torch.arange(L).float()
+    Mu = charbonneir(labels[None, :], labels[:, None], gamma)
+    return F.conv2d(x, Mu[..., None, None]) * torch.exp(s)
+
+
+def crf_as_rnn(refs, logits, gamma, s, niters, confidence=None, labels=None):
+    """crf_module.py:93-104 with W = BatchedAdjacency."""
+    if confidence is None:
+        confidence = 1
+    E0 = -logits * confidence
+    Q = F.softmax(-E0, dim=1)
+    for i in range(niters):
+        E = E0 + batched_adjacency(charb_forward(Q, gamma, s, labels), refs)
+        Q = F.softmax(-E, dim=1)
+    return -E
+
+
+def mean_field_infer(E_0, ref, Mu, niters=10):
+    """crf_module.py:41-53 with W = LatticeGaussian(ref) (gaussian_matrix.py:292-303)."""
+    Q = F.softmax(-E_0, dim=1)
+    for i in range(niters):
+        WQ = LatticeFilter.apply(Q, ref) - Q
+        E = E_0 + WQ @ Mu
+        Q = F.softmax(-E, dim=1)
+    return Q
+
+
+def ijrgb_guide(x, s_ij=.1, s_rgb=.1):
+    """crf_module.py:111-114."""
+    bs, c, h, w = x.shape
+    ij = torch.from_numpy(np.tile(np.mgrid[:h, :w] / np.sqrt(h ** 2 + w ** 2), (bs, 1, 1, 1))).float()
+    return torch.cat([ij / s_ij, x / s_rgb], dim=1)
+
+
+def logits2average_depth(logits, labels=None):
+    """mb_stereo_crf.py:62-66."""
+    probs = F.softmax(logits, dim=1)
+    if labels is None:
+        labels = torch.arange(probs.shape[1]).float()[None, :, None, None]
+    return (probs * labels).sum(1)[:, None, :, :]
