@@ -1,4 +1,5 @@
 // pl_api.cu -- extern "C" entry points of libpl_lattice.so (see include/pl_lattice.h).
+#include <math.h>
 #include <stdarg.h>
 #include <string.h>
 
@@ -74,6 +75,11 @@ static void lattice_release(Lattice* L, cudaStream_t st) {
   dev_free(L->rank, st);
   dev_free(L->vkeys, st);
   dev_free(L->nbr, st);
+  dev_free(L->ent_pix, st);
+  dev_free(L->ent_w, st);
+  dev_free(L->loc, st);
+  dev_free(L->useg, st);
+  dev_free(L->tile_off, st);
   dev_free(L->val[0], st);
   dev_free(L->val[1], st);
   delete L;
@@ -250,6 +256,28 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
     PL_CUDA(cudaMemcpyAsync(e_out_dev, e0_dev, sizeof(float) * (size_t)n * L,
                             cudaMemcpyDeviceToDevice, st));
     return PL_OK;
+  }
+  const bool aligned = (((uintptr_t)e0_dev | (uintptr_t)e_out_dev | (uintptr_t)work_dev |
+                         (uintptr_t)muT_dev) & 15u) == 0;
+  if (aligned && pl::mf_fused_supported(Lt, L) &&
+      !(flags & (PL_APPLY_FLAT_KERNELS | PL_APPLY_EXACT_SLICE | PL_MEANFIELD_UNFUSED))) {
+    // One kernel per iteration (pl_fused.cu): P lives in work_dev and is updated in place
+    // (a tile reads its own rows of P_prev into registers before it writes them).
+    PL_TRY(pl::lattice_workspace(Lt, L, st));
+    const size_t row = sizeof(float) * (size_t)L;
+    float* res = nullptr;           // buffer holding the blurred lattice of the previous iteration
+    PL_CUDA(cudaMemsetAsync(Lt->val[1] + (size_t)Lt->M * L, 0, row, st));
+    for (int it = 0; it < niters; it++) {
+      float* target = (res == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
+      float* other = (target == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
+      PL_CUDA(cudaMemsetAsync(target, 0, row * (size_t)(Lt->M + 1), st));
+      PL_TRY(pl::mf_fused_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, muT_dev,
+                                    scale, L, st));
+      PL_TRY(pl::lattice_blur(Lt, target, other, L, st, &res));
+    }
+    // E = E0 + (slice - P) of the last iteration (crf_module.py:101,103)
+    const float denom = 1 + powf(2, -Lt->d);
+    return pl::slice_tiled(Lt, res, L, denom, e_out_dev, L, work_dev, L, e0_dev, L, false, st);
   }
   for (int it = 0; it < niters; it++) {
     // P = scale * Mu softmax(-E)          crf_module.py:99-100,102 with :71-75

@@ -533,7 +533,7 @@ int build_impl(Lattice* L, const float* ref, cudaStream_t st) {
   dev_free(slot_vid, st);
   dev_free(table, st);
   dev_free(chunk_count, st);
-  return PL_OK;
+  return lattice_build_tiles(L, st);
 }
 
 }  // namespace

@@ -6,6 +6,7 @@
 
 #include "../../include/pl_lattice.h"
 
+#define PL_TILE 128      // points per lattice tile (pl_tiles.cu)
 #define PL_SM_COUNT 148  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
 
 namespace pl {
@@ -71,6 +72,14 @@ struct Lattice {
   int8_t* rank = nullptr;    // [n][d+1]
   int16_t* vkeys = nullptr;  // [M][d]
   int2* nbr = nullptr;       // [d+1][M] {minus, plus} neighbour ids; M = absent (zero row)
+  // tile-local view (pl_tiles.cu): per tile of PL_TILE points, entries sorted by vertex
+  int64_t ntiles = 0;
+  uint8_t* ent_pix = nullptr;  // [ntiles*TE] point index within the tile, sorted order
+  float* ent_w = nullptr;      // [ntiles*TE] barycentric weight, sorted order
+  uint16_t* loc = nullptr;     // [ntiles*TE] per original entry: index into the tile's vertex list
+  int2* useg = nullptr;        // per tile, per distinct vertex: {vertex id, start | count << 16}
+  int* tile_off = nullptr;     // [ntiles] offset of the tile's list in useg
+  int* tile_U = nullptr;       // [ntiles] distinct vertices in the tile (inside tile_off's block)
   // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats
   float* val[2] = {nullptr, nullptr};
   int64_t ws_floats = 0;     // floats per buffer
@@ -79,10 +88,24 @@ struct Lattice {
 
 // build (pl_build.cu)
 int lattice_build(Lattice* L, const float* ref, cudaStream_t st);
+// tile-local view + tiled kernels (pl_tiles.cu)
+int lattice_build_tiles(Lattice* L, cudaStream_t st);
+int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
+                cudaStream_t st);
+int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, int64_t dst_stride,
+                const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
+                bool exact, cudaStream_t st);
 // value path (pl_filter.cu)
 int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,
                   int C, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
                   uint32_t flags, cudaStream_t st);
+int lattice_workspace(Lattice* L, int Cc, cudaStream_t st);
+int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out);
+// fused mean-field iteration (pl_fused.cu)
+bool mf_fused_supported(const Lattice* L, int labels);
+int mf_fused_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
+                       const float* p_prev, float* p_next, const float* muT, float scale,
+                       int labels, cudaStream_t st);
 // mean field (pl_meanfield.cu)
 int softmax_compat(const float* e, const float* muT, float* p, float* q_out, int64_t n, int L,
                    float scale, cudaStream_t st);

@@ -198,8 +198,13 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
 
   const uint64_t pix_items = (uint64_t)n * (uint64_t)(Cc / VEC);
   const uint64_t vtx_items = (uint64_t)M * (uint64_t)(Cc / VEC);
-  PL_LAUNCH((splat_kernel<VEC, Idx>), grid_for(pix_items, 256, 8), 256, 0, st, src, src_stride, Cc,
-            L->vid, L->bary, D1, (Idx)n, cur);
+  const bool tiled = (VEC == 4) && !(flags & PL_APPLY_FLAT_KERNELS) && L->ntiles > 0;
+  if (tiled) {
+    PL_TRY(splat_tiled(L, src, src_stride, Cc, cur, st));
+  } else {
+    PL_LAUNCH((splat_kernel<VEC, Idx>), grid_for(pix_items, 256, 8), 256, 0, st, src, src_stride,
+              Cc, L->vid, L->bary, D1, (Idx)n, cur);
+  }
   for (int j = 0; j < D1; j++) {
     PL_LAUNCH((blur_kernel<VEC, Idx>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
               L->nbr + (size_t)j * M, (Idx)M, Cc);
@@ -208,7 +213,10 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
     nxt = t;
   }
   const float denom = 1 + powf(2, -L->d);  // permutohedral.h:480
-  if (flags & PL_APPLY_EXACT_SLICE) {
+  if (tiled) {
+    PL_TRY(slice_tiled(L, cur, Cc, denom, dst, dst_stride, sub, sub_stride, add, add_stride,
+                       (flags & PL_APPLY_EXACT_SLICE) != 0, st));
+  } else if (flags & PL_APPLY_EXACT_SLICE) {
     PL_LAUNCH((slice_kernel<VEC, true, Idx>), grid_for(pix_items, 256, 8), 256, 0, st, cur, Cc,
               L->vid, L->bary, D1, (Idx)n, denom, dst, dst_stride, sub, sub_stride, add,
               add_stride);
@@ -221,6 +229,43 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
 }
 
 }  // namespace
+
+// Grow-only ping-pong value buffers of (M+1) x Cc floats.
+int lattice_workspace(Lattice* L, int Cc, cudaStream_t st) {
+  const int64_t need = (L->M + 1) * (int64_t)Cc;
+  if (L->ws_floats >= need) return PL_OK;
+  for (int k = 0; k < 2; k++) {
+    if (L->val[k]) dev_free(L->val[k], st);
+    L->val[k] = nullptr;
+  }
+  L->ws_floats = 0;
+  PL_TRY(dev_alloc((void**)&L->val[0], sizeof(float) * (size_t)need, st));
+  PL_TRY(dev_alloc((void**)&L->val[1], sizeof(float) * (size_t)need, st));
+  L->ws_floats = need;
+  return PL_OK;
+}
+
+// d+1 Jacobi passes starting from `cur` (scratch `nxt`); *out = buffer holding the result.
+// Both buffers must have a zero row M.  Cc % 4 == 0.
+int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out) {
+  const int D1 = L->d + 1;
+  const int64_t M = L->M;
+  const uint64_t vtx_items = (uint64_t)M * (uint64_t)(Cc / 4);
+  for (int j = 0; j < D1; j++) {
+    if (vtx_items < 0x7fffffffull) {
+      PL_LAUNCH((blur_kernel<4, uint32_t>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
+                L->nbr + (size_t)j * M, (uint32_t)M, Cc);
+    } else {
+      PL_LAUNCH((blur_kernel<4, uint64_t>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
+                L->nbr + (size_t)j * M, (uint64_t)M, Cc);
+    }
+    float* t = cur;
+    cur = nxt;
+    nxt = t;
+  }
+  *out = cur;
+  return PL_OK;
+}
 
 int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,
                   int C, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
@@ -241,17 +286,7 @@ int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, 
   if (vec4) max_c &= ~(int64_t)3;
   const int chunk = (int)(C < max_c ? C : max_c);
 
-  const int64_t need = rows * chunk;
-  if (L->ws_floats < need) {
-    for (int k = 0; k < 2; k++) {
-      if (L->val[k]) dev_free(L->val[k], st);
-      L->val[k] = nullptr;
-    }
-    L->ws_floats = 0;
-    PL_TRY(dev_alloc((void**)&L->val[0], sizeof(float) * (size_t)need, st));
-    PL_TRY(dev_alloc((void**)&L->val[1], sizeof(float) * (size_t)need, st));
-    L->ws_floats = need;
-  }
+  PL_TRY(lattice_workspace(L, chunk, st));
 
   for (int c0 = 0; c0 < C; c0 += chunk) {
     const int Cc = (C - c0) < chunk ? (C - c0) : chunk;

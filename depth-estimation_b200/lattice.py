@@ -40,7 +40,7 @@ class PermutohedralLattice:
         self.num_vertices = int(N.lib().pl_lattice_num_vertices(self._h))
 
     # -- value path ---------------------------------------------------------
-    def filter(self, src, sub=None, add=None, exact_slice=False, out=None):
+    def filter(self, src, sub=None, add=None, exact_slice=False, out=None, flat=False):
         """``filter(src) - sub + add`` for ``src[n, C]`` (row stride may exceed C).
 
         ``sub=src`` is the adjacency ``W(x) = K x - x`` (gaussian_matrix.py:302,352);
@@ -67,7 +67,7 @@ class PermutohedralLattice:
                 t = _rowmajor(t)
                 ptrs.append(C.c_void_p(t.data_ptr()))
                 strides.append(t.stride(0))
-        flags = N.PL_APPLY_EXACT_SLICE if exact_slice else N.PL_APPLY_DEFAULT
+        flags = (N.PL_APPLY_EXACT_SLICE if exact_slice else 0) | (N.PL_APPLY_FLAT_KERNELS if flat else 0)
         with torch.cuda.device(self.device):
             N.check(N.lib().pl_lattice_apply(
                 self._h, C.c_void_p(src.data_ptr()), src.stride(0), C.c_void_p(out.data_ptr()),
@@ -77,7 +77,7 @@ class PermutohedralLattice:
 
     __call__ = filter
 
-    def mean_field(self, e0, mu, niters, scale=1.0, exact_slice=False):
+    def mean_field(self, e0, mu, niters, scale=1.0, exact_slice=False, flat=False, unfused=False):
         """Pixel-major CRFasRNN inference loop (crf_module.py:97-103).
 
         ``e0[n, L]`` unary energies, ``mu[L, L]`` compatibility matrix
@@ -92,7 +92,8 @@ class PermutohedralLattice:
         mu_t = mu.t().contiguous()
         out = torch.empty_like(e0)
         work = torch.empty_like(e0)
-        flags = N.PL_APPLY_EXACT_SLICE if exact_slice else N.PL_APPLY_DEFAULT
+        flags = ((N.PL_APPLY_EXACT_SLICE if exact_slice else 0) | (N.PL_APPLY_FLAT_KERNELS if flat else 0)
+                 | (N.PL_MEANFIELD_UNFUSED if unfused else 0))
         with torch.cuda.device(self.device):
             N.check(N.lib().pl_meanfield(
                 self._h, C.c_void_p(e0.data_ptr()), C.c_void_p(mu_t.data_ptr()),

@@ -77,6 +77,12 @@ int64_t pl_lattice_device_bytes(const pl_lattice* lat); /* persistent device mem
  * 1+2^-d, no FMA contraction) instead of folding the constant into the
  * barycentric weight. */
 #define PL_APPLY_EXACT_SLICE 1u
+/* Use the flat per-entry splat / slice kernels instead of the tile-local ones
+ * (pl_tiles.cu); for A/B measurements and tests. */
+#define PL_APPLY_FLAT_KERNELS 2u
+/* pl_meanfield only: run the separate softmax_compat / splat / blur / slice
+ * kernels instead of the fused per-iteration kernel (pl_fused.cu). */
+#define PL_MEANFIELD_UNFUSED 4u
 
 /* dst[p][c] = filter(src)[p][c] - (sub ? sub[p][c] : 0) + (add ? add[p][c] : 0)
  *

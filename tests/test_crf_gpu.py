@@ -178,3 +178,29 @@ def test_stereo_wrappers_run(native):
         out = refiner((torch.randn((1, 6, 24, 32), device="cuda"), torch.rand((1, 3, 24, 32), device="cuda"),
                        torch.randn((1, 8, 24, 32), device="cuda")))
     assert out.shape == (1, 1, 24, 32) and torch.isfinite(out).all()
+
+
+@pytest.mark.parametrize("h,w,L,niters,s_ij", [(37, 53, 4, 1, 0.1), (48, 64, 16, 5, 0.1), (50, 70, 40, 2, 0.1),
+                                                 (64, 96, 64, 3, 0.1), (40, 60, 64, 4, 0.01)])
+def test_fused_iteration_matches_unfused_and_oracle(native, oracle, h, w, L, niters, s_ij):
+    """pl_meanfield: fused per-iteration kernel (pl_fused.cu) vs separate kernels vs CPU oracle."""
+    ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=L), s_ij, 0.1)
+    e0 = synthetic.unary(h, w, L, seed=L)
+    mu = synthetic.charb_matrix(L) * 0.7
+    # oracle, pixel-major (crf_module.py:97-103 with W = filter - id)
+    hdl = oracle.build(ref)
+    e = e0.copy()
+    for _ in range(niters):
+        x = -e - (-e).max(1, keepdims=True)
+        q = np.exp(x) / np.exp(x).sum(1, keepdims=True)
+        p = (q @ mu.T).astype(np.float32) * np.float32(1.3)
+        e = e0 + (hdl.apply(p) - p)
+    lat = native.PermutohedralLattice(torch.from_numpy(ref).cuda())
+    e0d, mud = torch.from_numpy(e0).cuda(), torch.from_numpy(mu).cuda()
+    fused = lat.mean_field(e0d, mud, niters, 1.3).cpu().numpy()
+    unfused = lat.mean_field(e0d, mud, niters, 1.3, unfused=True).cpu().numpy()
+    flat = lat.mean_field(e0d, mud, niters, 1.3, flat=True).cpu().numpy()
+    scale = np.abs(e).max()
+    for got in (fused, unfused, flat):
+        assert np.abs(got - e).max() / scale < 2e-4
+        assert (got.argmin(1) == e.argmin(1)).mean() > 0.999

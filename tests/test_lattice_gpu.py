@@ -58,6 +58,9 @@ def test_random_features_match_oracle(native, oracle, n, d, C, scale):
     assert _relerr(got, want) < TOL
     got_exact = lat.filter(_cuda(src), exact_slice=True).cpu().numpy()
     assert _relerr(got_exact, want) < TOL
+    # flat per-entry kernels (A/B switch) agree with the tile-local ones
+    got_flat = lat.filter(_cuda(src), flat=True).cpu().numpy()
+    assert _relerr(got_flat, want) < TOL
     # one-shot entry point with the reference's call shape
     got2 = native.lattice.filter(_cuda(src), _cuda(ref)).cpu().numpy()
     assert _relerr(got2, want) < TOL
@@ -77,6 +80,8 @@ def test_image_features_match_oracle(native, oracle, h, w, s_ij, s_rgb, C):
     want = oracle.build(ref).apply(src)
     got = lat.filter(_cuda(src)).cpu().numpy()
     assert _relerr(got, want) < TOL
+    assert _relerr(lat.filter(_cuda(src), flat=True).cpu().numpy(), want) < TOL
+    assert _relerr(lat.filter(_cuda(src), exact_slice=True).cpu().numpy(), want) < TOL
 
 
 def test_matches_reference_itself_when_its_table_never_grows(native, reference):
