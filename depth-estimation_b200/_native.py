@@ -19,6 +19,7 @@ PL_APPLY_DEFAULT = 0
 PL_APPLY_EXACT_SLICE = 1
 PL_APPLY_FLAT_KERNELS = 2
 PL_MEANFIELD_UNFUSED = 4
+PL_MEANFIELD_NO_TENSOR = 8
 (PL_EXPORT_GREEDY, PL_EXPORT_RANK, PL_EXPORT_BARY, PL_EXPORT_VERTEX, PL_EXPORT_KEYS,
  PL_EXPORT_NEIGHBOURS) = range(6)
 
@@ -42,6 +43,8 @@ _SIGNATURES = {
                                  C.c_void_p]),
     "pl_softmax_compat": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.c_int, C.c_float, C.c_void_p]),
+    "pl_softmax_compat_ex": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                       C.c_int, C.c_float, C.c_uint32, C.c_void_p]),
     "pl_meanfield": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                C.c_int, C.c_float, C.c_uint32, C.c_void_p]),
     "pl_nchw_to_nlc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_float,
@@ -52,6 +55,7 @@ _SIGNATURES = {
     "pl_profile": (None, [C.c_int]),
     "pl_profile_report": (C.c_int, [C.c_char_p, C.c_int]),
     "pl_launch_count": (C.c_uint64, []),
+    "pl_debug_tc_timeouts": (C.c_int, []),
     "pl_version": (C.c_int, []),
     "pl_error_string": (C.c_char_p, [C.c_int]),
     "pl_last_error": (C.c_char_p, []),

@@ -237,9 +237,27 @@ int pl_filter_host(const float* src_host, const float* ref_host, float* dst_host
   return r;
 }
 
+int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
+                         int64_t n, int L, float scale, uint32_t flags, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool aligned = (((uintptr_t)e_dev | (uintptr_t)p_dev | (uintptr_t)q_out_dev) & 15u) == 0;
+  if (!(flags & PL_MEANFIELD_NO_TENSOR) && aligned && e_dev && muT_dev && p_dev && n > 0 &&
+      pl::mf_tc_supported(nullptr, L)) {
+    // tcgen05 path: Mu is split into tf32 hi / lo operand planes once, then one kernel
+    PL_TRY(pl::check_device());
+    float* mu_canon = nullptr;
+    PL_TRY(pl::dev_alloc((void**)&mu_canon, pl::mf_tc_mu_bytes(L), st));
+    int r = pl::mf_tc_prepare_mu(muT_dev, L, mu_canon, st);
+    if (r == PL_OK) r = pl::softmax_compat_tc(e_dev, mu_canon, p_dev, q_out_dev, n, L, scale, st);
+    pl::dev_free(mu_canon, st);
+    return r;
+  }
+  return pl::softmax_compat(e_dev, muT_dev, p_dev, q_out_dev, n, L, scale, st);
+}
+
 int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
                       int64_t n, int L, float scale, void* stream) {
-  return pl::softmax_compat(e_dev, muT_dev, p_dev, q_out_dev, n, L, scale, (cudaStream_t)stream);
+  return pl_softmax_compat_ex(e_dev, muT_dev, p_dev, q_out_dev, n, L, scale, 0u, stream);
 }
 
 int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, float* e_out_dev,
@@ -259,11 +277,19 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
   }
   const bool aligned = (((uintptr_t)e0_dev | (uintptr_t)e_out_dev | (uintptr_t)work_dev |
                          (uintptr_t)muT_dev) & 15u) == 0;
-  if (aligned && pl::mf_fused_supported(Lt, L) &&
-      !(flags & (PL_APPLY_FLAT_KERNELS | PL_APPLY_EXACT_SLICE | PL_MEANFIELD_UNFUSED))) {
-    // One kernel per iteration (pl_fused.cu): P lives in work_dev and is updated in place
-    // (a tile reads its own rows of P_prev into registers before it writes them).
+  const bool fusable = aligned && !(flags & (PL_APPLY_FLAT_KERNELS | PL_APPLY_EXACT_SLICE |
+                                             PL_MEANFIELD_UNFUSED));
+  const bool use_tc = fusable && !(flags & PL_MEANFIELD_NO_TENSOR) && pl::mf_tc_supported(Lt, L);
+  if (use_tc || (fusable && pl::mf_fused_supported(Lt, L))) {
+    // One kernel per iteration (pl_fused_tc.cu on the tensor cores, pl_fused.cu on the CUDA
+    // cores): P lives in work_dev and is updated in place (a tile reads its own rows of
+    // P_prev into registers before it writes them).
     PL_TRY(pl::lattice_workspace(Lt, L, st));
+    float* mu_canon = nullptr;
+    if (use_tc) {
+      PL_TRY(pl::dev_alloc((void**)&mu_canon, pl::mf_tc_mu_bytes(L), st));
+      PL_TRY(pl::mf_tc_prepare_mu(muT_dev, L, mu_canon, st));
+    }
     const size_t row = sizeof(float) * (size_t)L;
     float* res = nullptr;           // buffer holding the blurred lattice of the previous iteration
     PL_CUDA(cudaMemsetAsync(Lt->val[1] + (size_t)Lt->M * L, 0, row, st));
@@ -271,10 +297,16 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
       float* target = (res == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
       float* other = (target == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
       PL_CUDA(cudaMemsetAsync(target, 0, row * (size_t)(Lt->M + 1), st));
-      PL_TRY(pl::mf_fused_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, muT_dev,
-                                    scale, L, st));
+      if (use_tc) {
+        PL_TRY(pl::mf_tc_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
+                                   scale, L, st));
+      } else {
+        PL_TRY(pl::mf_fused_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev,
+                                      muT_dev, scale, L, st));
+      }
       PL_TRY(pl::lattice_blur(Lt, target, other, L, st, &res));
     }
+    pl::dev_free(mu_canon, st);
     // E = E0 + (slice - P) of the last iteration (crf_module.py:101,103)
     const float denom = 1 + powf(2, -Lt->d);
     return pl::slice_tiled(Lt, res, L, denom, e_out_dev, L, work_dev, L, e0_dev, L, false, st);
@@ -338,6 +370,7 @@ int pl_profile_report(char* buf, int cap) {
 }
 
 uint64_t pl_launch_count(void) { return pl::g_launches; }
+int pl_debug_tc_timeouts(void) { return pl::tc_timeouts(); }
 int pl_version(void) { return PL_VERSION; }
 
 const char* pl_error_string(int code) {

@@ -106,6 +106,16 @@ bool mf_fused_supported(const Lattice* L, int labels);
 int mf_fused_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
                        const float* p_prev, float* p_next, const float* muT, float scale,
                        int labels, cudaStream_t st);
+// fused mean-field iteration on the tensor cores (pl_fused_tc.cu), L in {16, 32, 64}
+bool mf_tc_supported(const Lattice* L, int labels);   // L == nullptr: stand-alone compat
+size_t mf_tc_mu_bytes(int labels);
+int mf_tc_prepare_mu(const float* muT, int labels, float* mu_canon, cudaStream_t st);
+int mf_tc_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
+                    const float* p_prev, float* p_next, const float* mu_canon, float scale,
+                    int labels, cudaStream_t st);
+int softmax_compat_tc(const float* e, const float* mu_canon, float* p, float* q_out, int64_t n,
+                      int labels, float scale, cudaStream_t st);
+int tc_timeouts();
 // mean field (pl_meanfield.cu)
 int softmax_compat(const float* e, const float* muT, float* p, float* q_out, int64_t n, int L,
                    float scale, cudaStream_t st);

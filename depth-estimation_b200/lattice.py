@@ -77,7 +77,8 @@ class PermutohedralLattice:
 
     __call__ = filter
 
-    def mean_field(self, e0, mu, niters, scale=1.0, exact_slice=False, flat=False, unfused=False):
+    def mean_field(self, e0, mu, niters, scale=1.0, exact_slice=False, flat=False, unfused=False,
+                   no_tensor=False):
         """Pixel-major CRFasRNN inference loop (crf_module.py:97-103).
 
         ``e0[n, L]`` unary energies, ``mu[L, L]`` compatibility matrix
@@ -93,7 +94,8 @@ class PermutohedralLattice:
         out = torch.empty_like(e0)
         work = torch.empty_like(e0)
         flags = ((N.PL_APPLY_EXACT_SLICE if exact_slice else 0) | (N.PL_APPLY_FLAT_KERNELS if flat else 0)
-                 | (N.PL_MEANFIELD_UNFUSED if unfused else 0))
+                 | (N.PL_MEANFIELD_UNFUSED if unfused else 0)
+                 | (N.PL_MEANFIELD_NO_TENSOR if no_tensor else 0))
         with torch.cuda.device(self.device):
             N.check(N.lib().pl_meanfield(
                 self._h, C.c_void_p(e0.data_ptr()), C.c_void_p(mu_t.data_ptr()),

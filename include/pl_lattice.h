@@ -83,6 +83,9 @@ int64_t pl_lattice_device_bytes(const pl_lattice* lat); /* persistent device mem
 /* pl_meanfield only: run the separate softmax_compat / splat / blur / slice
  * kernels instead of the fused per-iteration kernel (pl_fused.cu). */
 #define PL_MEANFIELD_UNFUSED 4u
+/* pl_meanfield / pl_softmax_compat: keep the compatibility transform on the CUDA cores
+ * (fp32 FMA, k ascending) instead of the tcgen05 3xTF32 path used for L in {16, 32, 64}. */
+#define PL_MEANFIELD_NO_TENSOR 8u
 
 /* dst[p][c] = filter(src)[p][c] - (sub ? sub[p][c] : 0) + (add ? add[p][c] : 0)
  *
@@ -118,6 +121,9 @@ int pl_filter_host(const float* src_host, const float* ref_host, float* dst_host
  * q_out_dev (optional, may be NULL) receives Q. */
 int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
                       int64_t n, int L, float scale, void* stream);
+/* Same with flags (PL_MEANFIELD_NO_TENSOR). */
+int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
+                         int64_t n, int L, float scale, uint32_t flags, void* stream);
 
 /* Whole inference loop of CRFasRNN.forward (crf_module.py:93-104) with
  * W = lattice adjacency (gaussian_matrix.py:341-352), pixel-major:
@@ -159,6 +165,9 @@ int pl_profile_report(char* buf, int cap);
 
 /* Number of kernels this library has launched in this process so far. */
 uint64_t pl_launch_count(void);
+/* Number of bounded mbarrier waits that timed out inside the tensor-core kernels since the
+ * library was loaded (0 unless something is badly wrong; synchronises the device). */
+int pl_debug_tc_timeouts(void);
 int pl_version(void);
 const char* pl_error_string(int code);
 const char* pl_last_error(void); /* detail of the most recent failure on this thread */

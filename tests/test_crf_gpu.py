@@ -48,6 +48,36 @@ def test_softmax_compat_kernel(native):
         assert _rel(p, want_p) < 1e-5
 
 
+@pytest.mark.parametrize("L", [16, 32, 64])
+def test_softmax_compat_tensor_core_path(native, L):
+    """tcgen05 3xTF32 compatibility transform (pl_fused_tc.cu, MODE 2) vs fp64 and vs the
+    CUDA-core kernel: full and ragged tiles, with and without the Q output."""
+    import ctypes as C
+    N = native._native
+    for n in (1, 127, 128, 129, 1000, 4099):
+        g = torch.Generator().manual_seed(L + n)
+        e = torch.randn((n, L), generator=g) * 3
+        mu = torch.from_numpy(synthetic.charb_matrix(L)) + torch.rand((L, L), generator=g) * 0.1
+        want_q = torch.softmax(-e.double(), dim=1)
+        want_p = (want_q @ mu.double().t()) * 1.7
+        ed, mt = e.cuda(), mu.t().contiguous().cuda()
+        outs = {}
+        for name, flags, with_q in (("tc", 0, True), ("tc_noq", 0, False),
+                                    ("cuda", N.PL_MEANFIELD_NO_TENSOR, True)):
+            p, q = torch.full_like(ed, float("nan")), torch.full_like(ed, float("nan"))
+            N.check(N.lib().pl_softmax_compat_ex(
+                C.c_void_p(ed.data_ptr()), C.c_void_p(mt.data_ptr()), C.c_void_p(p.data_ptr()),
+                C.c_void_p(q.data_ptr() if with_q else 0), n, L, 1.7, flags, N.stream_ptr(ed.device)))
+            torch.cuda.synchronize()
+            outs[name] = p
+            assert _rel(p.double(), want_p) < 2e-6, (name, n, L)
+            if with_q:
+                assert _rel(q.double(), want_q) < 2e-6
+        assert N.lib().pl_debug_tc_timeouts() == 0
+        # the split-TF32 result is as close to fp64 as the fp32 FMA chain is
+        assert _rel(outs["tc"], outs["cuda"]) < 4e-6
+
+
 def test_layout_helpers(native):
     import ctypes as C
     N = native._native
@@ -200,7 +230,9 @@ def test_fused_iteration_matches_unfused_and_oracle(native, oracle, h, w, L, nit
     fused = lat.mean_field(e0d, mud, niters, 1.3).cpu().numpy()
     unfused = lat.mean_field(e0d, mud, niters, 1.3, unfused=True).cpu().numpy()
     flat = lat.mean_field(e0d, mud, niters, 1.3, flat=True).cpu().numpy()
+    cuda_core = lat.mean_field(e0d, mud, niters, 1.3, no_tensor=True).cpu().numpy()
+    assert native._native.lib().pl_debug_tc_timeouts() == 0
     scale = np.abs(e).max()
-    for got in (fused, unfused, flat):
+    for got in (fused, unfused, flat, cuda_core):
         assert np.abs(got - e).max() / scale < 2e-4
         assert (got.argmin(1) == e.argmin(1)).mean() > 0.999
