@@ -80,6 +80,8 @@ static void lattice_release(Lattice* L, cudaStream_t st) {
   dev_free(L->loc, st);
   dev_free(L->useg, st);
   dev_free(L->tile_off, st);
+  dev_free(L->rec_slice, st);
+  dev_free(L->rec_splat, st);
   dev_free(L->val[0], st);
   dev_free(L->val[1], st);
   delete L;

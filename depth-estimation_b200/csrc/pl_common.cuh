@@ -80,6 +80,11 @@ struct Lattice {
   int2* useg = nullptr;        // per tile, per distinct vertex: {vertex id, start | count << 16}
   int* tile_off = nullptr;     // [ntiles] offset of the tile's list in useg
   int* tile_U = nullptr;       // [ntiles] distinct vertices in the tile (inside tile_off's block)
+  // the same lists packed per tile for single bulk (TMA) copies, pads zeroed (pl_fused_tc.cu):
+  //   rec_slice[tile] = { bary f32[TE] | loc u16[TE] }                      (entry order)
+  //   rec_splat[tile] = { ent_w f32[TE] | vertex id i32[TE] | ent_pix u8[TE] }  (sorted order)
+  uint8_t* rec_slice = nullptr;
+  uint8_t* rec_splat = nullptr;
   // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats
   float* val[2] = {nullptr, nullptr};
   int64_t ws_floats = 0;     // floats per buffer

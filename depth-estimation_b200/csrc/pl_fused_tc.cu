@@ -32,7 +32,7 @@ namespace {
 
 constexpr int kTile = PL_TILE;   // 128 pixels = UMMA M
 constexpr int kThreads = 256;
-constexpr int kStageRows = 144;  // lattice rows staged per tile
+constexpr int kCtasPerSm = 2;
 
 __device__ int g_tc_timeouts = 0;
 
@@ -41,7 +41,7 @@ constexpr int cmax(int a, int b) { return a > b ? a : b; }
 template <int L>
 struct Cfg {
   static constexpr int V = L / 4;               // float4 lanes per pixel row (4 / 8 / 16)
-  static constexpr int RPP = kThreads / V;      // rows per pass
+  static constexpr int RPP = kThreads / V;      // rows per pass = lane groups per CTA
   static constexpr int RPT = kTile / RPP;       // rows per thread (2 / 4 / 8)
   static constexpr int KCH = L / 4;             // 16-byte K chunks per operand row
   static constexpr int A_CH = kTile * 16 + 16;  // bytes per K chunk of A (padded)
@@ -50,7 +50,8 @@ struct Cfg {
   static constexpr int B_BYTES = KCH * B_CH;
   static constexpr int PLD = L + 4;             // P row pitch in floats
   static constexpr int QA_BYTES = cmax(2 * A_BYTES, kTile * PLD * 4);
-  static constexpr int R_BYTES = cmax(kStageRows * L * 4, 2 * B_BYTES);
+  // lattice rows staged per tile: what fits under the Q planes, at most one per thread
+  static constexpr int STAGE_ROWS = QA_BYTES / (L * 4) < kThreads ? QA_BYTES / (L * 4) : kThreads;
   static constexpr int TMEM_COLS = L < 32 ? 32 : L;
 };
 
@@ -64,13 +65,12 @@ struct MfArgs {
   const float* mu_canon; // Mu hi / lo planes in the canonical operand layout
   float scale;
   int64_t n;
+  int64_t ntiles;
   int d1;
   float inv_denom;
-  const uint16_t* loc;
-  const float* bary;
-  const int32_t* vid;
-  const uint8_t* ent_pix;
-  const float* ent_w;
+  const int32_t* vid;        // [n][d1]            (fallback when a tile has too many vertices)
+  const uint8_t* rec_slice;  // per tile { bary f32[TE] | loc u16[TE] }
+  const uint8_t* rec_splat;  // per tile { w f32[TE] | vertex i32[TE] | pixel u8[TE] }
   const int2* useg;
   const int* tile_off;
   const int* tile_U;
@@ -78,8 +78,7 @@ struct MfArgs {
 
 __device__ __forceinline__ void red_add_v4(float* addr, float4 x) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(x.x), "f"(x.y),
-               "f"(x.z), "f"(x.w)
-               : "memory");
+               "f"(x.z), "f"(x.w));
 }
 
 template <int W>
@@ -97,39 +96,57 @@ __device__ __forceinline__ float group_sum(float v) {
 
 // MODE 0: first iteration (E = E0, splat P)   MODE 1: later iteration (slice, splat P)
 // MODE 2: stand-alone softmax + compatibility (no lattice)
-template <int L, int MODE>
-__global__ void __launch_bounds__(kThreads, 2) mf_tc_kernel(const MfArgs a) {
+// D1T: d + 1 known at compile time (6 for the 5-D stereo guide) or 0 = run-time.
+//
+// Persistent: each CTA walks tiles blockIdx.x, +gridDim.x, ...  Per tile
+//   [lists land by TMA] -> stage lattice rows -> slice -> softmax -> Q planes -> MMAs ->
+//   TMEM -> P tile -> HBM + splat
+// while the NEXT tile's E0 / P_prev rows (registers), slice lists (TMA) and distinct-vertex
+// ids (registers) are already in flight; Mu is fetched once per CTA.
+template <int L, int MODE, int D1T>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm) mf_tc_kernel(const MfArgs a) {
   using C = Cfg<L>;
   constexpr int V = C::V, RPP = C::RPP, RPT = C::RPT;
   extern __shared__ __align__(128) unsigned char smem[];
-  unsigned char* s_qa = smem;                          // Q hi | Q lo operand planes; later P
-  unsigned char* s_r = smem + C::QA_BYTES;             // staged lattice rows; later Mu hi | lo
-  const int d1 = a.d1;
+  const int d1 = D1T > 0 ? D1T : a.d1;
   const int TE = (MODE == 2) ? 0 : kTile * d1;
-  float* s_w = reinterpret_cast<float*>(s_r + C::R_BYTES);   // [TE] slice weights (entry order)
-  int* s_idx = reinterpret_cast<int*>(s_w + TE);             // [TE] slice row (local or global)
-  float* s_sw = reinterpret_cast<float*>(s_idx + TE);        // [TE] splat weights (sorted)
-  uint8_t* s_spix = reinterpret_cast<uint8_t*>(s_sw + TE);   // [TE] splat pixel (sorted)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(
-      smem + ((C::QA_BYTES + C::R_BYTES + 13 * TE + 15) & ~15));  // [0] Mu landed, [1] MMAs done
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  unsigned char* s_qa = smem;                       // lattice rows -> Q hi | lo planes -> P tile
+  unsigned char* s_mu = smem + C::QA_BYTES;         // Mu hi | lo planes (whole kernel)
+  unsigned char* s_rs = s_mu + 2 * C::B_BYTES;      // slice record  { bary | loc }
+  unsigned char* s_rp = s_rs + 6 * TE;              // splat record  { w | vertex | pixel }
+  int* s_uvid = reinterpret_cast<int*>(s_rp + 9 * TE);          // [256] distinct vertex ids
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_uvid + (MODE == 2 ? 0 : kThreads));
+  // bars: [0] Mu landed  [1] MMAs done  [2] slice record landed  [3] splat record landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const float* s_bary = reinterpret_cast<const float*>(s_rs);
+  const uint16_t* s_loc = reinterpret_cast<const uint16_t*>(s_rs + 4 * TE);
+  const float* s_sw = reinterpret_cast<const float*>(s_rp);
+  const int* s_ev = reinterpret_cast<const int*>(s_rp + 4 * TE);
+  const uint8_t* s_spix = s_rp + 8 * TE;
+  const float* s_val = reinterpret_cast<const float*>(s_qa);
+  float* s_p = reinterpret_cast<float*>(s_qa);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int64_t tile = blockIdx.x;
-  const int64_t p0 = tile * kTile;
-  const int rows = (int)min((int64_t)kTile, a.n - p0);
   const int g = tid / V, l = tid % V;
-  const float* s_val = reinterpret_cast<const float*>(s_r);
+  int64_t tile = blockIdx.x;
+  if (tile >= a.ntiles) return;  // (grid never exceeds ntiles; keeps the setup below uniform)
 
-  // ---- one-time setup: barriers, TMEM, (MODE 0 / 2) Mu fetch ----------------------------
+  // ---- one-time setup: barriers, TMEM, Mu and the first tile's lists ---------------------
   if (warp == 0) {
     if (lane == 0) {
-      tc::mbar_init(&bars[0], 1);
-      tc::mbar_init(&bars[1], 1);
+#pragma unroll
+      for (int b = 0; b < 4; b++) tc::mbar_init(&bars[b], 1);
       tc::fence_mbar_init();
-      if (MODE != 1) {  // region R is free from the start: fetch Mu while the softmax runs
-        tc::mbar_arrive_expect_tx(&bars[0], 2 * C::B_BYTES);
-        tc::tma_load_1d(s_r, a.mu_canon, 2 * C::B_BYTES, &bars[0]);
+      tc::mbar_arrive_expect_tx(&bars[0], 2 * C::B_BYTES);
+      tc::tma_load_1d(s_mu, a.mu_canon, 2 * C::B_BYTES, &bars[0]);
+      if (MODE == 1) {
+        tc::mbar_arrive_expect_tx(&bars[2], 6 * TE);
+        tc::tma_load_1d(s_rs, a.rec_slice + tile * (int64_t)(6 * TE), 6 * TE, &bars[2]);
+      }
+      if (MODE != 2) {
+        tc::mbar_arrive_expect_tx(&bars[3], 9 * TE);
+        tc::tma_load_1d(s_rp, a.rec_splat + tile * (int64_t)(9 * TE), 9 * TE, &bars[3]);
       }
     }
     __syncwarp();
@@ -137,173 +154,238 @@ __global__ void __launch_bounds__(kThreads, 2) mf_tc_kernel(const MfArgs a) {
     tc::tcgen05_fence_before();
   }
 
-  int U = 0;
-  const int2* seg = nullptr;
-  bool staged = false;
-  if (MODE != 2) {
-    U = a.tile_U[tile];
-    seg = a.useg + a.tile_off[tile];
-    staged = U <= kStageRows;
-    const int valid = rows * d1;
-    for (int i = tid; i < valid; i += kThreads) {
-      s_sw[i] = a.ent_w[tile * TE + i];
-      s_spix[i] = a.ent_pix[tile * TE + i];
-      if (MODE == 1) {
-        s_w[i] = a.bary[tile * TE + i] * a.inv_denom;
-        s_idx[i] = staged ? (int)a.loc[tile * TE + i] : a.vid[tile * TE + i];
-      }
-    }
-    if (MODE == 1 && staged) {
-      float* sv = reinterpret_cast<float*>(s_r);
-      for (int i = tid; i < U * V; i += kThreads) {
-        const int u = i / V, v = i - u * V;
-        *reinterpret_cast<float4*>(sv + u * L + 4 * v) =
-            *reinterpret_cast<const float4*>(a.val_in + (int64_t)seg[u].x * L + 4 * v);
-      }
-    }
-  }
-  // this thread's E0 / P_prev vectors, in flight while the staging loads land
+  // first tile's E0 / P_prev rows and distinct-vertex id -> registers
   float4 e_reg[RPT], pp_reg[RPT];
+  int U = 0, my_uvid = 0;
+  auto prefetch = [&](int64_t t) {
+    const int64_t q0 = t * kTile;
+    const int nrows = (int)min((int64_t)kTile, a.n - q0);
 #pragma unroll
-  for (int i = 0; i < RPT; i++) {
-    const int r = g + i * RPP;
-    e_reg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    pp_reg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r < rows) {
-      e_reg[i] = *reinterpret_cast<const float4*>(a.e0 + (p0 + r) * L + 4 * l);
-      if (MODE == 1) pp_reg[i] = *reinterpret_cast<const float4*>(a.p_prev + (p0 + r) * L + 4 * l);
+    for (int i = 0; i < RPT; i++) {
+      const int r = g + i * RPP;
+      e_reg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      pp_reg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < nrows) {
+        e_reg[i] = *reinterpret_cast<const float4*>(a.e0 + (q0 + r) * L + 4 * l);
+        if (MODE == 1)
+          pp_reg[i] = *reinterpret_cast<const float4*>(a.p_prev + (q0 + r) * L + 4 * l);
+      }
     }
-  }
+    if (MODE == 1) {
+      U = a.tile_U[t];
+      my_uvid = (tid < U) ? a.useg[a.tile_off[t] + tid].x : 0;
+    }
+  };
+  prefetch(tile);
   __syncthreads();
   tc::tcgen05_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  // ---- slice + energy + softmax -> Q hi / lo operand planes ------------------------------
-#pragma unroll
-  for (int i = 0; i < RPT; i++) {
-    const int r = g + i * RPP;
-    const bool live = r < rows;
-    float4 e = e_reg[i];
-    if (MODE == 1 && live) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int j = 0; j < d1; j++) {
-        const float w = s_w[r * d1 + j];
-        const int ix = s_idx[r * d1 + j];
-        const float4 x = staged
-                             ? *reinterpret_cast<const float4*>(s_val + ix * L + 4 * l)
-                             : *reinterpret_cast<const float4*>(a.val_in + (int64_t)ix * L + 4 * l);
-        acc.x = __fmaf_rn(w, x.x, acc.x);
-        acc.y = __fmaf_rn(w, x.y, acc.y);
-        acc.z = __fmaf_rn(w, x.z, acc.z);
-        acc.w = __fmaf_rn(w, x.w, acc.w);
-      }
-      // E = E0 + (filtered - P)   (crf_module.py:101, gaussian_matrix.py:352)
-      e.x = __fadd_rn(e.x, __fsub_rn(acc.x, pp_reg[i].x));
-      e.y = __fadd_rn(e.y, __fsub_rn(acc.y, pp_reg[i].y));
-      e.z = __fadd_rn(e.z, __fsub_rn(acc.z, pp_reg[i].z));
-      e.w = __fadd_rn(e.w, __fsub_rn(acc.w, pp_reg[i].w));
-    }
-    float m = live ? fmaxf(fmaxf(-e.x, -e.y), fmaxf(-e.z, -e.w)) : -INFINITY;
-    m = group_max<V>(m);
-    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (live) {
-      x.x = expf(-e.x - m);
-      x.y = expf(-e.y - m);
-      x.z = expf(-e.z - m);
-      x.w = expf(-e.w - m);
-    }
-    const float s = group_sum<V>(x.x + x.y + x.z + x.w);
-    const float inv = live ? 1.0f / s : 0.f;
-    x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
-    if (MODE == 2 && a.q_out != nullptr && live)
-      *reinterpret_cast<float4*>(a.q_out + (p0 + r) * L + 4 * l) = x;
-    float4 hi, lo;
-    hi.x = tc::tf32_rna(x.x); lo.x = tc::tf32_rna(x.x - hi.x);
-    hi.y = tc::tf32_rna(x.y); lo.y = tc::tf32_rna(x.y - hi.y);
-    hi.z = tc::tf32_rna(x.z); lo.z = tc::tf32_rna(x.z - hi.z);
-    hi.w = tc::tf32_rna(x.w); lo.w = tc::tf32_rna(x.w - hi.w);
-    // K chunk l, row r of the canonical A layout
-    *reinterpret_cast<float4*>(s_qa + l * C::A_CH + r * 16) = hi;
-    *reinterpret_cast<float4*>(s_qa + C::A_BYTES + l * C::A_CH + r * 16) = lo;
-  }
-  tc::fence_proxy_async();  // Q planes (generic proxy) -> visible to the tensor core's reads
-  __syncthreads();          // also: nobody reads the staged lattice rows any more
+  for (uint32_t it = 0; tile < a.ntiles; tile += gridDim.x, it++) {
+    const uint32_t par = it & 1;
+    const int64_t p0 = tile * kTile;
+    const int rows = (int)min((int64_t)kTile, a.n - p0);
+    const int valid = rows * d1;
+    const int64_t next = tile + gridDim.x;
+    const bool has_next = next < a.ntiles;
 
-  // ---- P = Q Mu^T on the tensor cores: one thread issues ---------------------------------
-  if (tid == 0) {
+    // ---- slice: E = E0 + (slice(blurred lattice) - P_prev) --------------------------------
     if (MODE == 1) {
-      tc::mbar_arrive_expect_tx(&bars[0], 2 * C::B_BYTES);
-      tc::tma_load_1d(s_r, a.mu_canon, 2 * C::B_BYTES, &bars[0]);
-    }
-    if (!tc::mbar_wait(&bars[0], 0)) atomicAdd(&g_tc_timeouts, 1);
-    tc::tcgen05_fence_after();
-    constexpr uint32_t idesc = tc::idesc_tf32(kTile, L);
-    const uint32_t a_hi = tc::smem_u32(s_qa), a_lo = a_hi + C::A_BYTES;
-    const uint32_t b_hi = tc::smem_u32(s_r), b_lo = b_hi + C::B_BYTES;
+      const bool staged = U <= C::STAGE_ROWS;
+      if (staged) {
+        s_uvid[tid] = my_uvid;
+        __syncthreads();
+        // rows of the tile's distinct vertices: V lanes per row, coalesced 16-byte pieces
+        float* sv = reinterpret_cast<float*>(s_qa);
+        for (int u = g; u < U; u += RPP)
+          *reinterpret_cast<float4*>(sv + u * L + 4 * l) =
+              *reinterpret_cast<const float4*>(a.val_in + (int64_t)s_uvid[u] * L + 4 * l);
+      }
+      if (!tc::mbar_wait(&bars[2], par)) atomicAdd(&g_tc_timeouts, 1);
+      __syncthreads();
 #pragma unroll
-    for (int pass = 0; pass < 3; pass++) {  // lo*hi, hi*lo, hi*hi
-      const uint32_t ab = (pass == 0) ? a_lo : a_hi;
-      const uint32_t bb = (pass == 1) ? b_lo : b_hi;
+      for (int i = 0; i < RPT; i++) {
+        const int r = g + i * RPP;
+        if (r < rows) {
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int ks = 0; ks < L / 8; ks++) {  // K = 8 per instruction = two 16-byte chunks
-        const uint64_t ad = tc::smem_desc_kmajor(ab + ks * 2 * C::A_CH, C::A_CH, 128);
-        const uint64_t bd = tc::smem_desc_kmajor(bb + ks * 2 * C::B_CH, C::B_CH, 128);
-        tc::mma_tf32_ss(tmem, ad, bd, idesc, (pass | ks) != 0);
+          for (int j = 0; j < (D1T > 0 ? D1T : d1); j++) {
+            const float w = s_bary[r * d1 + j];
+            const float4 x =
+                staged ? *reinterpret_cast<const float4*>(s_val + (int)s_loc[r * d1 + j] * L + 4 * l)
+                       : *reinterpret_cast<const float4*>(
+                             a.val_in + (int64_t)a.vid[p0 * d1 + r * d1 + j] * L + 4 * l);
+            acc.x = __fmaf_rn(w, x.x, acc.x);
+            acc.y = __fmaf_rn(w, x.y, acc.y);
+            acc.z = __fmaf_rn(w, x.z, acc.z);
+            acc.w = __fmaf_rn(w, x.w, acc.w);
+          }
+          // E = E0 + (filtered / (1 + 2^-d) - P)   (crf_module.py:101, gaussian_matrix.py:352)
+          e_reg[i].x = __fadd_rn(e_reg[i].x, __fmaf_rn(acc.x, a.inv_denom, -pp_reg[i].x));
+          e_reg[i].y = __fadd_rn(e_reg[i].y, __fmaf_rn(acc.y, a.inv_denom, -pp_reg[i].y));
+          e_reg[i].z = __fadd_rn(e_reg[i].z, __fmaf_rn(acc.z, a.inv_denom, -pp_reg[i].z));
+          e_reg[i].w = __fadd_rn(e_reg[i].w, __fmaf_rn(acc.w, a.inv_denom, -pp_reg[i].w));
+        }
+      }
+      __syncthreads();  // staged rows and the slice record are dead
+      if (tid == 0 && has_next) {
+        tc::mbar_arrive_expect_tx(&bars[2], 6 * TE);
+        tc::tma_load_1d(s_rs, a.rec_slice + next * (int64_t)(6 * TE), 6 * TE, &bars[2]);
       }
     }
-    tc::mma_commit(&bars[1]);
-  }
-  __syncwarp();
-  if (!tc::mbar_wait(&bars[1], 0)) atomicAdd(&g_tc_timeouts, 1);
-  __syncwarp();
-  tc::tcgen05_fence_after();
 
-  // ---- epilogue: TMEM -> registers -> P tile in shared memory (over the dead Q planes) ---
-  float* s_p = reinterpret_cast<float*>(s_qa);
-  {
-    const int q = warp & 3, hsel = warp >> 2;  // TMEM lane quarter, column half
-    const int row = q * 32 + lane;
+    // ---- softmax(-E) -> Q hi / lo operand planes ------------------------------------------
+    {
+      float m[RPT];
 #pragma unroll
-    for (int c8 = 0; c8 < (L / 2) / 8; c8++) {
-      const int col = hsel * (L / 2) + c8 * 8;
-      float v[8];
-      tc::tmem_ld_x8(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)col, v);
-      float4 o0 = make_float4(v[0] * a.scale, v[1] * a.scale, v[2] * a.scale, v[3] * a.scale);
-      float4 o1 = make_float4(v[4] * a.scale, v[5] * a.scale, v[6] * a.scale, v[7] * a.scale);
-      *reinterpret_cast<float4*>(s_p + row * C::PLD + col) = o0;
-      *reinterpret_cast<float4*>(s_p + row * C::PLD + col + 4) = o1;
+      for (int i = 0; i < RPT; i++) {
+        const float4 e = e_reg[i];
+        m[i] = (g + i * RPP < rows) ? fmaxf(fmaxf(-e.x, -e.y), fmaxf(-e.z, -e.w)) : -INFINITY;
+      }
+#pragma unroll
+      for (int o = V / 2; o > 0; o >>= 1)
+#pragma unroll
+        for (int i = 0; i < RPT; i++) m[i] = fmaxf(m[i], __shfl_xor_sync(0xffffffffu, m[i], o, V));
+      float s[RPT];
+#pragma unroll
+      for (int i = 0; i < RPT; i++) {
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g + i * RPP < rows) {
+          x.x = expf(-e_reg[i].x - m[i]);
+          x.y = expf(-e_reg[i].y - m[i]);
+          x.z = expf(-e_reg[i].z - m[i]);
+          x.w = expf(-e_reg[i].w - m[i]);
+        }
+        e_reg[i] = x;
+        s[i] = x.x + x.y + x.z + x.w;
+      }
+#pragma unroll
+      for (int o = V / 2; o > 0; o >>= 1)
+#pragma unroll
+        for (int i = 0; i < RPT; i++) s[i] += __shfl_xor_sync(0xffffffffu, s[i], o, V);
+#pragma unroll
+      for (int i = 0; i < RPT; i++) {
+        const int r = g + i * RPP;
+        const float inv = (r < rows) ? 1.0f / s[i] : 0.f;
+        float4 x = e_reg[i];
+        x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
+        if (MODE == 2 && a.q_out != nullptr && r < rows)
+          *reinterpret_cast<float4*>(a.q_out + (p0 + r) * L + 4 * l) = x;
+        float4 hi, lo;
+        hi.x = tc::tf32_rna(x.x); lo.x = tc::tf32_rna(x.x - hi.x);
+        hi.y = tc::tf32_rna(x.y); lo.y = tc::tf32_rna(x.y - hi.y);
+        hi.z = tc::tf32_rna(x.z); lo.z = tc::tf32_rna(x.z - hi.z);
+        hi.w = tc::tf32_rna(x.w); lo.w = tc::tf32_rna(x.w - hi.w);
+        // K chunk l, row r of the canonical A layout
+        *reinterpret_cast<float4*>(s_qa + l * C::A_CH + r * 16) = hi;
+        *reinterpret_cast<float4*>(s_qa + C::A_BYTES + l * C::A_CH + r * 16) = lo;
+      }
+    }
+    tc::fence_proxy_async();  // Q planes (generic proxy) -> visible to the tensor core's reads
+    __syncthreads();
+
+    // ---- P = Q Mu^T on the tensor cores: one thread issues --------------------------------
+    if (tid == 0) {
+      if (it == 0 && !tc::mbar_wait(&bars[0], 0)) atomicAdd(&g_tc_timeouts, 1);
+      tc::tcgen05_fence_after();
+      constexpr uint32_t idesc = tc::idesc_tf32(kTile, L);
+      const uint32_t a_hi = tc::smem_u32(s_qa), a_lo = a_hi + C::A_BYTES;
+      const uint32_t b_hi = tc::smem_u32(s_mu), b_lo = b_hi + C::B_BYTES;
+#pragma unroll
+      for (int pass = 0; pass < 3; pass++) {  // lo*hi, hi*lo, hi*hi
+        const uint32_t ab = (pass == 0) ? a_lo : a_hi;
+        const uint32_t bb = (pass == 1) ? b_lo : b_hi;
+#pragma unroll
+        for (int ks = 0; ks < L / 8; ks++) {  // K = 8 per instruction = two 16-byte chunks
+          const uint64_t ad = tc::smem_desc_kmajor(ab + ks * 2 * C::A_CH, C::A_CH, 128);
+          const uint64_t bd = tc::smem_desc_kmajor(bb + ks * 2 * C::B_CH, C::B_CH, 128);
+          tc::mma_tf32_ss(tmem, ad, bd, idesc, (pass | ks) != 0);
+        }
+      }
+      tc::mma_commit(&bars[1]);
+    }
+    // the next tile's inputs start their trip while the MMAs, the epilogue and the splat run
+    if (has_next) prefetch(next);
+    __syncwarp();
+    if (!tc::mbar_wait(&bars[1], par)) atomicAdd(&g_tc_timeouts, 1);
+    __syncwarp();
+    tc::tcgen05_fence_after();
+
+    // ---- epilogue: TMEM -> registers -> P tile in shared memory (over the dead Q planes) --
+    {
+      const int q = warp & 3, hsel = warp >> 2;  // TMEM lane quarter, column half
+      const int row = q * 32 + lane;
+#pragma unroll
+      for (int c8 = 0; c8 < (L / 2) / 8; c8++) {
+        const int col = hsel * (L / 2) + c8 * 8;
+        float v[8];
+        tc::tmem_ld_x8(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)col, v);
+        float4 o0 = make_float4(v[0] * a.scale, v[1] * a.scale, v[2] * a.scale, v[3] * a.scale);
+        float4 o1 = make_float4(v[4] * a.scale, v[5] * a.scale, v[6] * a.scale, v[7] * a.scale);
+        *reinterpret_cast<float4*>(s_p + row * C::PLD + col) = o0;
+        *reinterpret_cast<float4*>(s_p + row * C::PLD + col + 4) = o1;
+      }
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+
+    // ---- P -> HBM (coalesced rows) --------------------------------------------------------
+#pragma unroll
+    for (int i = 0; i < RPT; i++) {
+      const int r = g + i * RPP;
+      if (r < rows)
+        *reinterpret_cast<float4*>(a.p_next + (p0 + r) * L + 4 * l) =
+            *reinterpret_cast<const float4*>(s_p + r * C::PLD + 4 * l);
+    }
+
+    // ---- splat P: every lane group walks a contiguous range of the vertex-sorted entries,
+    //      keeps a running sum and flushes one red.global.add.v4 per (vertex, range) ----------
+    if (MODE != 2) {
+      if (!tc::mbar_wait(&bars[3], par)) atomicAdd(&g_tc_timeouts, 1);
+      const int cpg = (((valid + RPP - 1) / RPP) + 3) & ~3;  // entries per group, multiple of 4
+      const int k0 = g * cpg, k1 = min(valid, k0 + cpg);
+      if (k0 < k1) {
+        int cur = s_ev[k0];
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = k0; k < k1; k += 4) {  // pads beyond `valid` carry weight 0, vertex 0
+          const int4 ev = *reinterpret_cast<const int4*>(s_ev + k);
+          const float4 ew = *reinterpret_cast<const float4*>(s_sw + k);
+          const uchar4 ep = *reinterpret_cast<const uchar4*>(s_spix + k);
+          const float4 x0 = *reinterpret_cast<const float4*>(s_p + (int)ep.x * C::PLD + 4 * l);
+          const float4 x1 = *reinterpret_cast<const float4*>(s_p + (int)ep.y * C::PLD + 4 * l);
+          const float4 x2 = *reinterpret_cast<const float4*>(s_p + (int)ep.z * C::PLD + 4 * l);
+          const float4 x3 = *reinterpret_cast<const float4*>(s_p + (int)ep.w * C::PLD + 4 * l);
+#define PL_SPLAT_STEP(VV, WW, XX, KK)                                         \
+  if ((KK) < k1) {                                                            \
+    if ((VV) != cur) {                                                        \
+      red_add_v4(a.val_out + (int64_t)cur * L + 4 * l, acc);                  \
+      acc = make_float4(0.f, 0.f, 0.f, 0.f);                                  \
+      cur = (VV);                                                             \
+    }                                                                         \
+    acc.x = __fmaf_rn((WW), (XX).x, acc.x);                                   \
+    acc.y = __fmaf_rn((WW), (XX).y, acc.y);                                   \
+    acc.z = __fmaf_rn((WW), (XX).z, acc.z);                                   \
+    acc.w = __fmaf_rn((WW), (XX).w, acc.w);                                   \
+  }
+          PL_SPLAT_STEP(ev.x, ew.x, x0, k)
+          PL_SPLAT_STEP(ev.y, ew.y, x1, k + 1)
+          PL_SPLAT_STEP(ev.z, ew.z, x2, k + 2)
+          PL_SPLAT_STEP(ev.w, ew.w, x3, k + 3)
+#undef PL_SPLAT_STEP
+        }
+        red_add_v4(a.val_out + (int64_t)cur * L + 4 * l, acc);
+      }
+    }
+    __syncthreads();  // P tile and splat record are dead: the next tile may overwrite them
+    if (MODE != 2 && tid == 0 && has_next) {
+      tc::mbar_arrive_expect_tx(&bars[3], 9 * TE);
+      tc::tma_load_1d(s_rp, a.rec_splat + next * (int64_t)(9 * TE), 9 * TE, &bars[3]);
     }
   }
+
   tc::tcgen05_fence_before();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc(tmem, C::TMEM_COLS);
-
-  // ---- P -> HBM (coalesced rows) ----------------------------------------------------------
-#pragma unroll
-  for (int i = 0; i < RPT; i++) {
-    const int r = g + i * RPP;
-    if (r < rows)
-      *reinterpret_cast<float4*>(a.p_next + (p0 + r) * L + 4 * l) =
-          *reinterpret_cast<const float4*>(s_p + r * C::PLD + 4 * l);
-  }
-
-  // ---- splat P: segment sums per distinct vertex of the tile -----------------------------
-  if (MODE != 2) {
-    for (int u = g; u < U; u += RPP) {
-      const int2 sg = seg[u];
-      const int st = sg.y & 0xFFFF, cnt = sg.y >> 16;
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int k = st; k < st + cnt; k++) {
-        const float w = s_sw[k];
-        const float4 x = *reinterpret_cast<const float4*>(s_p + (int)s_spix[k] * C::PLD + 4 * l);
-        acc.x = __fmaf_rn(w, x.x, acc.x);
-        acc.y = __fmaf_rn(w, x.y, acc.y);
-        acc.z = __fmaf_rn(w, x.z, acc.z);
-        acc.w = __fmaf_rn(w, x.w, acc.w);
-      }
-      red_add_v4(a.val_out + (int64_t)sg.x * L + 4 * l, acc);
-    }
-  }
 }
 
 // Mu[l][k] = muT[k][l] -> hi / lo planes in the canonical K-major operand layout
@@ -330,32 +412,39 @@ template <int L>
 size_t tc_smem(int d1, bool lattice) {
   using C = Cfg<L>;
   const int TE = lattice ? kTile * d1 : 0;
-  return (size_t)((C::QA_BYTES + C::R_BYTES + 13 * TE + 15) & ~15) + 32;
+  return (size_t)C::QA_BYTES + 2 * C::B_BYTES + 15 * (size_t)TE + (lattice ? 4 * kThreads : 0) + 64;
 }
 
-template <int L, int MODE>
-int launch_tc(const MfArgs& a, unsigned grid, cudaStream_t st) {
+template <int L, int MODE, int D1T>
+int launch_tc(const MfArgs& a, cudaStream_t st) {
   const size_t smem = tc_smem<L>(a.d1, MODE != 2);
   static size_t attr_smem = 0;
   if (smem > attr_smem) {
-    PL_CUDA(cudaFuncSetAttribute(mf_tc_kernel<L, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smem));
+    PL_CUDA(cudaFuncSetAttribute((mf_tc_kernel<L, MODE, D1T>),
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_smem = smem;
   }
-  PL_LAUNCH((mf_tc_kernel<L, MODE>), grid, kThreads, smem, st, a);
+  const int64_t cap = (int64_t)PL_SM_COUNT * (smem <= 113 * 1024 ? kCtasPerSm : 1);
+  const unsigned grid = (unsigned)(a.ntiles < cap ? a.ntiles : cap);
+  PL_LAUNCH((mf_tc_kernel<L, MODE, D1T>), grid, kThreads, smem, st, a);
   return PL_OK;
 }
 
 template <int MODE>
-int dispatch_tc(int L, const MfArgs& a, unsigned grid, cudaStream_t st) {
+int dispatch_tc(int L, const MfArgs& a, cudaStream_t st) {
+#define PL_TC_CASE(LL)                                                   \
+  case LL:                                                               \
+    if (MODE != 2 && a.d1 == 6) return launch_tc<LL, MODE, 6>(a, st);    \
+    return launch_tc<LL, MODE, 0>(a, st);
   switch (L) {
-    case 16: return launch_tc<16, MODE>(a, grid, st);
-    case 32: return launch_tc<32, MODE>(a, grid, st);
-    case 64: return launch_tc<64, MODE>(a, grid, st);
+    PL_TC_CASE(16)
+    PL_TC_CASE(32)
+    PL_TC_CASE(64)
     default:
       set_last_error("tensor-core mean-field kernel: unsupported label count %d", L);
       return PL_ERR_INVALID;
   }
+#undef PL_TC_CASE
 }
 
 size_t tc_smem_for(int L, int d1, bool lattice) {
@@ -372,7 +461,8 @@ size_t tc_smem_for(int L, int d1, bool lattice) {
 bool mf_tc_supported(const Lattice* L, int labels) {
   if (labels != 16 && labels != 32 && labels != 64) return false;
   if (L == nullptr) return true;  // stand-alone softmax + compatibility
-  return L->ntiles > 0 && tc_smem_for(labels, L->d + 1, true) <= 200 * 1024;
+  return L->ntiles > 0 && L->rec_slice != nullptr &&
+         tc_smem_for(labels, L->d + 1, true) <= 200 * 1024;
 }
 
 size_t mf_tc_mu_bytes(int labels) { return 2 * (size_t)(labels / 4) * (labels * 16 + 16); }
@@ -386,14 +476,15 @@ int mf_tc_prepare_mu(const float* muT, int labels, float* mu_canon, cudaStream_t
 int mf_tc_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
                     const float* p_prev, float* p_next, const float* mu_canon, float scale,
                     int labels, cudaStream_t st) {
-  MfArgs a;
+  MfArgs a = {};
   a.val_in = val_in; a.val_out = val_out; a.e0 = e0; a.p_prev = p_prev; a.p_next = p_next;
-  a.q_out = nullptr; a.mu_canon = mu_canon; a.scale = scale; a.n = L->n; a.d1 = L->d + 1;
+  a.q_out = nullptr; a.mu_canon = mu_canon; a.scale = scale; a.n = L->n; a.ntiles = L->ntiles;
+  a.d1 = L->d + 1;
   a.inv_denom = 1.0f / (1 + powf(2, -L->d));
-  a.loc = L->loc; a.bary = L->bary; a.vid = L->vid; a.ent_pix = L->ent_pix; a.ent_w = L->ent_w;
+  a.vid = L->vid; a.rec_slice = L->rec_slice; a.rec_splat = L->rec_splat;
   a.useg = L->useg; a.tile_off = L->tile_off; a.tile_U = L->tile_U;
-  if (first) return dispatch_tc<0>(labels, a, (unsigned)L->ntiles, st);
-  return dispatch_tc<1>(labels, a, (unsigned)L->ntiles, st);
+  if (first) return dispatch_tc<0>(labels, a, st);
+  return dispatch_tc<1>(labels, a, st);
 }
 
 // P = scale * softmax(-E) Mu^T without a lattice (pl_softmax_compat), optional Q output.
@@ -401,8 +492,9 @@ int softmax_compat_tc(const float* e, const float* mu_canon, float* p, float* q_
                       int labels, float scale, cudaStream_t st) {
   MfArgs a = {};
   a.e0 = e; a.p_next = p; a.q_out = q_out; a.mu_canon = mu_canon; a.scale = scale; a.n = n;
+  a.ntiles = (n + kTile - 1) / kTile;
   a.d1 = 0;
-  return dispatch_tc<2>(labels, a, ceil_div_u((uint64_t)n, kTile), st);
+  return dispatch_tc<2>(labels, a, st);
 }
 
 int tc_timeouts() {

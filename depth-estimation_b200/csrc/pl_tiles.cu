@@ -35,7 +35,8 @@ __global__ void __launch_bounds__(kThreads)
 tile_build_kernel(const int32_t* __restrict__ vid, const float* __restrict__ bary, int64_t n,
                   int d1, int NS, uint8_t* __restrict__ ent_pix, float* __restrict__ ent_w,
                   uint16_t* __restrict__ loc, int2* __restrict__ useg, int* __restrict__ tile_off,
-                  int* __restrict__ tile_U, int* __restrict__ counter) {
+                  int* __restrict__ tile_U, int* __restrict__ counter,
+                  uint8_t* __restrict__ rec_slice, uint8_t* __restrict__ rec_splat) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);   // [NS]
   unsigned short* ustart = reinterpret_cast<unsigned short*>(keys + NS);        // [TE + 1]
@@ -47,6 +48,12 @@ tile_build_kernel(const int32_t* __restrict__ vid, const float* __restrict__ bar
   const int64_t tile = blockIdx.x;
   const int64_t e0 = tile * TE;
   const int64_t E = n * d1;
+  // packed per-tile records (see pl_common.cuh); pads (k >= valid) are written as zeros
+  float* rs_bary = reinterpret_cast<float*>(rec_slice + tile * (int64_t)TE * 6);
+  uint16_t* rs_loc = reinterpret_cast<uint16_t*>(rs_bary + TE);
+  float* rp_w = reinterpret_cast<float*>(rec_splat + tile * (int64_t)TE * 9);
+  int32_t* rp_vid = reinterpret_cast<int32_t*>(rp_w + TE);
+  uint8_t* rp_pix = reinterpret_cast<uint8_t*>(rp_vid + TE);
 
   for (int k = tid; k < NS; k += kThreads) {
     unsigned long long key = kPad;
@@ -104,19 +111,36 @@ tile_build_kernel(const int32_t* __restrict__ vid, const float* __restrict__ bar
     const int64_t rem = E - e0;
     valid = rem < TE ? (int)rem : TE;
   }
+  for (int i = valid + tid; i < TE; i += kThreads) {
+    rs_bary[i] = 0.f;
+    rs_loc[i] = 0;
+  }
   for (int q = 0; q < PER; q++) {
     const int k = base + q;
     const unsigned long long key = keys[k];
-    if (key == kPad) continue;
+    if (key == kPad) {
+      if (k < TE) {
+        rp_w[k] = 0.f;
+        rp_vid[k] = 0;
+        rp_pix[k] = 0;
+      }
+      continue;
+    }
     const bool head = (k == 0 || (keys[k - 1] >> 16) != (key >> 16));
     if (head) {
       ustart[u] = (unsigned short)k;
       u++;
     }
     const int orig = (int)(key & 0xFFFFu);
+    const float wgt = bary[e0 + orig];
     ent_pix[e0 + k] = (uint8_t)(orig / d1);
-    ent_w[e0 + k] = bary[e0 + orig];
+    ent_w[e0 + k] = wgt;
     loc[e0 + orig] = (uint16_t)(u - 1);
+    rp_w[k] = wgt;
+    rp_vid[k] = (int32_t)(key >> 16);
+    rp_pix[k] = (uint8_t)(orig / d1);
+    rs_bary[orig] = wgt;
+    rs_loc[orig] = (uint16_t)(u - 1);
   }
   if (tid == 0) {
     ustart[U] = (unsigned short)valid;
@@ -155,14 +179,17 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   L->tile_U = L->tile_off + ntiles;
   int* counter = L->tile_off + 2 * ntiles;
   L->ntiles = ntiles;
-  L->bytes += (int64_t)(E_pad * (1 + 4 + 2 + 8) + sizeof(int) * (size_t)(2 * ntiles + 1));
+  PL_TRY(dev_alloc((void**)&L->rec_slice, E_pad * 6, st));
+  PL_TRY(dev_alloc((void**)&L->rec_splat, E_pad * 9, st));
+  L->bytes += (int64_t)(E_pad * (1 + 4 + 2 + 8 + 6 + 9) + sizeof(int) * (size_t)(2 * ntiles + 1));
   PL_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), st));
   const size_t smem = sizeof(unsigned long long) * NS + sizeof(unsigned short) * (TE + 2);
   if (smem > 48 * 1024)
     PL_CUDA(cudaFuncSetAttribute(tile_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem));
   PL_LAUNCH(tile_build_kernel, (unsigned)ntiles, kThreads, smem, st, L->vid, L->bary, L->n, d1, NS,
-            L->ent_pix, L->ent_w, L->loc, L->useg, L->tile_off, L->tile_U, counter);
+            L->ent_pix, L->ent_w, L->loc, L->useg, L->tile_off, L->tile_U, counter, L->rec_slice,
+            L->rec_splat);
   return PL_OK;
 }
 
