@@ -203,23 +203,48 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) mf_tc_kernel(const MfArg
       }
       if (!tc::mbar_wait(&bars[2], par)) atomicAdd(&g_tc_timeouts, 1);
       __syncthreads();
+#define PL_SLICE_FMA(WW, XX)            \
+  acc.x = __fmaf_rn((WW), (XX).x, acc.x); \
+  acc.y = __fmaf_rn((WW), (XX).y, acc.y); \
+  acc.z = __fmaf_rn((WW), (XX).z, acc.z); \
+  acc.w = __fmaf_rn((WW), (XX).w, acc.w);
 #pragma unroll
       for (int i = 0; i < RPT; i++) {
         const int r = g + i * RPP;
         if (r < rows) {
           float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-          for (int j = 0; j < (D1T > 0 ? D1T : d1); j++) {
-            const float w = s_bary[r * d1 + j];
-            const float4 x =
-                staged ? *reinterpret_cast<const float4*>(s_val + (int)s_loc[r * d1 + j] * L + 4 * l)
-                       : *reinterpret_cast<const float4*>(
-                             a.val_in + (int64_t)a.vid[p0 * d1 + r * d1 + j] * L + 4 * l);
-            acc.x = __fmaf_rn(w, x.x, acc.x);
-            acc.y = __fmaf_rn(w, x.y, acc.y);
-            acc.z = __fmaf_rn(w, x.z, acc.z);
-            acc.w = __fmaf_rn(w, x.w, acc.w);
+          if (staged) {
+            if (D1T == 6) {
+              // six (weight, row) pairs of this pixel: 3 x LDS.64 + 3 x LDS.32 (broadcast)
+              const float2* wp = reinterpret_cast<const float2*>(s_bary + r * 6);
+              const uint32_t* lp = reinterpret_cast<const uint32_t*>(s_loc + r * 6);
+              const float2 w01 = wp[0], w23 = wp[1], w45 = wp[2];
+              const uint32_t l01 = lp[0], l23 = lp[1], l45 = lp[2];
+              const float4 x0 = *reinterpret_cast<const float4*>(s_val + (l01 & 0xFFFF) * L + 4 * l);
+              const float4 x1 = *reinterpret_cast<const float4*>(s_val + (l01 >> 16) * L + 4 * l);
+              const float4 x2 = *reinterpret_cast<const float4*>(s_val + (l23 & 0xFFFF) * L + 4 * l);
+              const float4 x3 = *reinterpret_cast<const float4*>(s_val + (l23 >> 16) * L + 4 * l);
+              const float4 x4 = *reinterpret_cast<const float4*>(s_val + (l45 & 0xFFFF) * L + 4 * l);
+              const float4 x5 = *reinterpret_cast<const float4*>(s_val + (l45 >> 16) * L + 4 * l);
+              PL_SLICE_FMA(w01.x, x0) PL_SLICE_FMA(w01.y, x1) PL_SLICE_FMA(w23.x, x2)
+              PL_SLICE_FMA(w23.y, x3) PL_SLICE_FMA(w45.x, x4) PL_SLICE_FMA(w45.y, x5)
+            } else {
+              for (int j = 0; j < d1; j++) {
+                const float w = s_bary[r * d1 + j];
+                const float4 x =
+                    *reinterpret_cast<const float4*>(s_val + (int)s_loc[r * d1 + j] * L + 4 * l);
+                PL_SLICE_FMA(w, x)
+              }
+            }
+          } else {  // too many distinct vertices to stage: rows straight from L2
+            for (int j = 0; j < d1; j++) {
+              const float w = s_bary[r * d1 + j];
+              const float4 x = *reinterpret_cast<const float4*>(
+                  a.val_in + (int64_t)a.vid[(p0 + r) * d1 + j] * L + 4 * l);
+              PL_SLICE_FMA(w, x)
+            }
           }
+#undef PL_SLICE_FMA
           // E = E0 + (filtered / (1 + 2^-d) - P)   (crf_module.py:101, gaussian_matrix.py:352)
           e_reg[i].x = __fadd_rn(e_reg[i].x, __fmaf_rn(acc.x, a.inv_denom, -pp_reg[i].x));
           e_reg[i].y = __fadd_rn(e_reg[i].y, __fmaf_rn(acc.y, a.inv_denom, -pp_reg[i].y));
@@ -251,10 +276,10 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) mf_tc_kernel(const MfArg
       for (int i = 0; i < RPT; i++) {
         float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
         if (g + i * RPP < rows) {
-          x.x = expf(-e_reg[i].x - m[i]);
-          x.y = expf(-e_reg[i].y - m[i]);
-          x.z = expf(-e_reg[i].z - m[i]);
-          x.w = expf(-e_reg[i].w - m[i]);
+          x.x = __expf(-e_reg[i].x - m[i]);
+          x.y = __expf(-e_reg[i].y - m[i]);
+          x.z = __expf(-e_reg[i].z - m[i]);
+          x.w = __expf(-e_reg[i].w - m[i]);
         }
         e_reg[i] = x;
         s[i] = x.x + x.y + x.z + x.w;
@@ -266,7 +291,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) mf_tc_kernel(const MfArg
 #pragma unroll
       for (int i = 0; i < RPT; i++) {
         const int r = g + i * RPP;
-        const float inv = (r < rows) ? 1.0f / s[i] : 0.f;
+        const float inv = (r < rows) ? __fdividef(1.0f, s[i]) : 0.f;
         float4 x = e_reg[i];
         x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
         if (MODE == 2 && a.q_out != nullptr && r < rows)
@@ -313,17 +338,22 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) mf_tc_kernel(const MfArg
 
     // ---- epilogue: TMEM -> registers -> P tile in shared memory (over the dead Q planes) --
     {
-      const int q = warp & 3, hsel = warp >> 2;  // TMEM lane quarter, column half
+      // TMEM lane quarter q (a warp can only read lanes 32*(warp%4)..+31) x column group
+      constexpr int NCG = (kThreads / 128) < (L / 8) ? (kThreads / 128) : (L / 8);
+      constexpr int CPW = L / NCG;  // columns per warp, multiple of 8
+      const int q = warp & 3, hsel = warp >> 2;
       const int row = q * 32 + lane;
+      if (hsel < NCG) {
 #pragma unroll
-      for (int c8 = 0; c8 < (L / 2) / 8; c8++) {
-        const int col = hsel * (L / 2) + c8 * 8;
-        float v[8];
-        tc::tmem_ld_x8(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)col, v);
-        float4 o0 = make_float4(v[0] * a.scale, v[1] * a.scale, v[2] * a.scale, v[3] * a.scale);
-        float4 o1 = make_float4(v[4] * a.scale, v[5] * a.scale, v[6] * a.scale, v[7] * a.scale);
-        *reinterpret_cast<float4*>(s_p + row * C::PLD + col) = o0;
-        *reinterpret_cast<float4*>(s_p + row * C::PLD + col + 4) = o1;
+        for (int c8 = 0; c8 < CPW / 8; c8++) {
+          const int col = hsel * CPW + c8 * 8;
+          float v[8];
+          tc::tmem_ld_x8(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)col, v);
+          float4 o0 = make_float4(v[0] * a.scale, v[1] * a.scale, v[2] * a.scale, v[3] * a.scale);
+          float4 o1 = make_float4(v[4] * a.scale, v[5] * a.scale, v[6] * a.scale, v[7] * a.scale);
+          *reinterpret_cast<float4*>(s_p + row * C::PLD + col) = o0;
+          *reinterpret_cast<float4*>(s_p + row * C::PLD + col + 4) = o1;
+        }
       }
     }
     tc::tcgen05_fence_before();
@@ -343,7 +373,8 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) mf_tc_kernel(const MfArg
     if (MODE != 2) {
       if (!tc::mbar_wait(&bars[3], par)) atomicAdd(&g_tc_timeouts, 1);
       const int cpg = (((valid + RPP - 1) / RPP) + 3) & ~3;  // entries per group, multiple of 4
-      const int k0 = g * cpg, k1 = min(valid, k0 + cpg);
+      // the record's pads (entries >= valid) carry weight 0 and vertex 0: no bounds check inside
+      const int k0 = g * cpg, k1 = min((valid + 3) & ~3, k0 + cpg);
       if (k0 < k1) {
         int cur = s_ev[k0];
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -356,7 +387,7 @@ __global__ void __launch_bounds__(kThreads, kCtasPerSm) mf_tc_kernel(const MfArg
           const float4 x2 = *reinterpret_cast<const float4*>(s_p + (int)ep.z * C::PLD + 4 * l);
           const float4 x3 = *reinterpret_cast<const float4*>(s_p + (int)ep.w * C::PLD + 4 * l);
 #define PL_SPLAT_STEP(VV, WW, XX, KK)                                         \
-  if ((KK) < k1) {                                                            \
+  {                                                                           \
     if ((VV) != cur) {                                                        \
       red_add_v4(a.val_out + (int64_t)cur * L + 4 * l, acc);                  \
       acc = make_float4(0.f, 0.f, 0.f, 0.f);                                  \
