@@ -295,10 +295,11 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
     const size_t row = sizeof(float) * (size_t)L;
     float* res = nullptr;           // buffer holding the blurred lattice of the previous iteration
     PL_CUDA(cudaMemsetAsync(Lt->val[1] + (size_t)Lt->M * L, 0, row, st));
+    PL_CUDA(cudaMemsetAsync(Lt->val[0], 0, row * (size_t)(Lt->M + 1), st));
     for (int it = 0; it < niters; it++) {
+      // the splat target: zeroed above (first iteration) or by the previous blur
       float* target = (res == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
       float* other = (target == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
-      PL_CUDA(cudaMemsetAsync(target, 0, row * (size_t)(Lt->M + 1), st));
       if (use_tc) {
         PL_TRY(pl::mf_tc_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
                                    scale, L, st));
@@ -306,7 +307,7 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
         PL_TRY(pl::mf_fused_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev,
                                       muT_dev, scale, L, st));
       }
-      PL_TRY(pl::lattice_blur(Lt, target, other, L, st, &res));
+      PL_TRY(pl::lattice_blur(Lt, target, other, L, st, &res, it + 1 < niters));
     }
     pl::dev_free(mu_canon, st);
     // E = E0 + (slice - P) of the last iteration (crf_module.py:101,103)

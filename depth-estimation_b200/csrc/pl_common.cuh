@@ -105,7 +105,8 @@ int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, 
                   int C, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
                   uint32_t flags, cudaStream_t st);
 int lattice_workspace(Lattice* L, int Cc, cudaStream_t st);
-int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out);
+int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out,
+                 bool zero_other = false);
 // fused mean-field iteration (pl_fused.cu)
 bool mf_fused_supported(const Lattice* L, int labels);
 int mf_fused_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,

@@ -12,6 +12,7 @@
 // Very wide value matrices (the backward pass filters 2L(1+d) channels,
 // crf/gaussian_matrix.py:450-458) are processed in channel chunks so the two
 // ping-pong lattice buffers stay bounded; the lattice itself is reused.
+#include <cooperative_groups.h>
 #include <math.h>
 
 #include "pl_common.cuh"
@@ -181,6 +182,113 @@ slice_kernel(const float* __restrict__ val, int Cc, const int32_t* __restrict__ 
   }
 }
 
+// All d+1 axes in ONE cooperative launch: a grid-wide barrier separates the Jacobi passes
+// (the lattice of a stereo frame is a few MB, L2 resident; 6 launches of a few microseconds
+// each were launch-bound).  Optionally zeroes the buffer that does NOT hold the result, which
+// is the next mean-field iteration's splat target.
+template <typename Idx>
+__global__ void __launch_bounds__(256)
+blur_all_kernel(float* __restrict__ buf0, float* __restrict__ buf1, const int2* __restrict__ nbr,
+                Idx M, int Cc, int D1, int zero_other) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  const Idx V = (Idx)(Cc / 4);
+  const Idx total = M * V;
+  float* in = buf0;
+  float* out = buf1;
+  for (int j = 0; j < D1; j++) {
+    const int2* nbr_j = nbr + (size_t)j * M;
+    for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (Idx)gridDim.x * blockDim.x) {
+      const Idx v = t / V;
+      const int c = (int)(t - v * V) * 4;
+      const int2 nb = nbr_j[v];
+      const float4 o = __ldcg(reinterpret_cast<const float4*>(in + (int64_t)v * Cc + c));
+      const float4 a = __ldcg(reinterpret_cast<const float4*>(in + (int64_t)nb.x * Cc + c));
+      const float4 b = __ldcg(reinterpret_cast<const float4*>(in + (int64_t)nb.y * Cc + c));
+      float4 r;
+      r.x = __fmaf_rn(0.5f, b.x, __fmaf_rn(0.5f, a.x, o.x));
+      r.y = __fmaf_rn(0.5f, b.y, __fmaf_rn(0.5f, a.y, o.y));
+      r.z = __fmaf_rn(0.5f, b.z, __fmaf_rn(0.5f, a.z, o.z));
+      r.w = __fmaf_rn(0.5f, b.w, __fmaf_rn(0.5f, a.w, o.w));
+      *reinterpret_cast<float4*>(out + (int64_t)v * Cc + c) = r;
+    }
+    grid.sync();
+    float* t2 = in;
+    in = out;
+    out = t2;
+  }
+  if (zero_other) {  // `in` holds the result; `out` is free
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (Idx)gridDim.x * blockDim.x)
+      *reinterpret_cast<float4*>(out + (int64_t)t * 4) = z;
+  }
+}
+
+// Small lattices (a stereo frame with the module's default guide scales has M ~ 10^4
+// vertices, a few MB of values): every thread owns ITEMS (vertex, float4) items for the whole
+// blur.  Its 2(d+1) neighbour offsets are fetched once, its own value stays in registers
+// across the axes, so a pass is two L2 gathers + one store + the grid barrier.  d = 5 only.
+constexpr int kBlurRegThreads = 512;
+template <int ITEMS>
+__global__ void __launch_bounds__(kBlurRegThreads, 2)
+blur_reg_kernel(float* __restrict__ buf0, float* __restrict__ buf1, const int2* __restrict__ nbr,
+                uint32_t M, int Cc, int zero_other) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  constexpr int D1 = 6;
+  const uint32_t V = (uint32_t)(Cc / 4);
+  const uint32_t total = M * V;
+  uint32_t off[ITEMS], na[ITEMS][D1], nb[ITEMS][D1];
+  float4 val[ITEMS];
+  bool live[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) {
+    const uint32_t t = ((uint32_t)blockIdx.x * ITEMS + i) * kBlurRegThreads + threadIdx.x;
+    live[i] = t < total;
+    const uint32_t v = live[i] ? t / V : 0;
+    const uint32_t c = live[i] ? (t - v * V) * 4 : 0;
+    off[i] = v * (uint32_t)Cc + c;
+#pragma unroll
+    for (int j = 0; j < D1; j++) {
+      const int2 p = nbr[(size_t)j * M + v];
+      na[i][j] = (uint32_t)p.x * (uint32_t)Cc + c;
+      nb[i][j] = (uint32_t)p.y * (uint32_t)Cc + c;
+    }
+    val[i] = live[i] ? __ldcg(reinterpret_cast<const float4*>(buf0 + off[i]))
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  float* in = buf0;
+  float* out = buf1;
+#pragma unroll
+  for (int j = 0; j < D1; j++) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      if (live[i]) {
+        const float4 a = __ldcg(reinterpret_cast<const float4*>(in + na[i][j]));
+        const float4 b = __ldcg(reinterpret_cast<const float4*>(in + nb[i][j]));
+        float4 r;
+        r.x = __fmaf_rn(0.5f, b.x, __fmaf_rn(0.5f, a.x, val[i].x));
+        r.y = __fmaf_rn(0.5f, b.y, __fmaf_rn(0.5f, a.y, val[i].y));
+        r.z = __fmaf_rn(0.5f, b.z, __fmaf_rn(0.5f, a.z, val[i].z));
+        r.w = __fmaf_rn(0.5f, b.w, __fmaf_rn(0.5f, a.w, val[i].w));
+        *reinterpret_cast<float4*>(out + off[i]) = r;
+        val[i] = r;
+      }
+    }
+    grid.sync();
+    float* t2 = in;
+    in = out;
+    out = t2;
+  }
+  if (zero_other) {  // `in` holds the result (D1 is even: buf0); `out` is free
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++)
+      if (live[i]) *reinterpret_cast<float4*>(out + off[i]) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
 bool aligned16(const void* p) { return ((uintptr_t)p & 15u) == 0; }
 
 template <int VEC, typename Idx>
@@ -205,12 +313,18 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
     PL_LAUNCH((splat_kernel<VEC, Idx>), grid_for(pix_items, 256, 8), 256, 0, st, src, src_stride,
               Cc, L->vid, L->bary, D1, (Idx)n, cur);
   }
-  for (int j = 0; j < D1; j++) {
-    PL_LAUNCH((blur_kernel<VEC, Idx>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
-              L->nbr + (size_t)j * M, (Idx)M, Cc);
-    float* t = cur;
-    cur = nxt;
-    nxt = t;
+  if (VEC == 4) {
+    float* res = nullptr;
+    PL_TRY(lattice_blur(L, cur, nxt, Cc, st, &res));
+    cur = res;
+  } else {
+    for (int j = 0; j < D1; j++) {
+      PL_LAUNCH((blur_kernel<VEC, Idx>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
+                L->nbr + (size_t)j * M, (Idx)M, Cc);
+      float* t = cur;
+      cur = nxt;
+      nxt = t;
+    }
   }
   const float denom = 1 + powf(2, -L->d);  // permutohedral.h:480
   if (tiled) {
@@ -247,23 +361,74 @@ int lattice_workspace(Lattice* L, int Cc, cudaStream_t st) {
 
 // d+1 Jacobi passes starting from `cur` (scratch `nxt`); *out = buffer holding the result.
 // Both buffers must have a zero row M.  Cc % 4 == 0.
-int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out) {
+int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out,
+                 bool zero_other) {
   const int D1 = L->d + 1;
   const int64_t M = L->M;
   const uint64_t vtx_items = (uint64_t)M * (uint64_t)(Cc / 4);
+  // one cooperative launch for all axes (all CTAs must be co-resident)
+  static int coop_ctas_per_sm = -1;
+  if (coop_ctas_per_sm < 0) {
+    int dev = 0, coop = 0, occ = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (coop &&
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, blur_all_kernel<uint32_t>, 256, 0) ==
+            cudaSuccess)
+      coop_ctas_per_sm = occ > 4 ? 4 : occ;
+    else
+      coop_ctas_per_sm = 0;
+  }
+  // register-resident variant: d = 5 and at most 2 items per thread on 2 x 148 CTAs
+  if (coop_ctas_per_sm > 0 && D1 == 6 && (uint64_t)(M + 1) * Cc < 0x7fffffffull &&
+      vtx_items <= (uint64_t)PL_SM_COUNT * 2 * kBlurRegThreads * 2) {
+    const int items = vtx_items <= (uint64_t)PL_SM_COUNT * 2 * kBlurRegThreads ? 1 : 2;
+    unsigned grid = ceil_div_u(vtx_items, (uint64_t)kBlurRegThreads * items);
+    uint32_t M32 = (uint32_t)M;
+    int zo = zero_other ? 1 : 0;
+    const int2* nbr = L->nbr;
+    void* args[] = {&cur, &nxt, &nbr, &M32, &Cc, &zo};
+    const void* fn = items == 1 ? (const void*)blur_reg_kernel<1> : (const void*)blur_reg_kernel<2>;
+    if (g_prof_on) prof_begin("blur_reg_kernel", st);
+    cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kBlurRegThreads), args, 0, st);
+    if (g_prof_on) prof_end(st);
+    g_launches++;
+    PL_CUDA(e);
+    *out = cur;  // six passes: back in the buffer it started from
+    return PL_OK;
+  }
+  if (coop_ctas_per_sm > 0 && vtx_items < 0x7fffffffull) {
+    unsigned grid = grid_for(vtx_items, 256, (unsigned)coop_ctas_per_sm);
+    uint32_t M32 = (uint32_t)M;
+    int zo = zero_other ? 1 : 0;
+    int d1 = D1;
+    const int2* nbr = L->nbr;
+    void* args[] = {&cur, &nxt, &nbr, &M32, &Cc, &d1, &zo};
+    if (g_prof_on) prof_begin("blur_all_kernel", st);
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)blur_all_kernel<uint32_t>, dim3(grid),
+                                                dim3(256), args, 0, st);
+    if (g_prof_on) prof_end(st);
+    g_launches++;
+    PL_CUDA(e);
+    *out = (D1 & 1) ? nxt : cur;
+    return PL_OK;
+  }
+  float* a = cur;
+  float* b = nxt;
   for (int j = 0; j < D1; j++) {
     if (vtx_items < 0x7fffffffull) {
-      PL_LAUNCH((blur_kernel<4, uint32_t>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
+      PL_LAUNCH((blur_kernel<4, uint32_t>), grid_for(vtx_items, 256, 8), 256, 0, st, a, b,
                 L->nbr + (size_t)j * M, (uint32_t)M, Cc);
     } else {
-      PL_LAUNCH((blur_kernel<4, uint64_t>), grid_for(vtx_items, 256, 8), 256, 0, st, cur, nxt,
+      PL_LAUNCH((blur_kernel<4, uint64_t>), grid_for(vtx_items, 256, 8), 256, 0, st, a, b,
                 L->nbr + (size_t)j * M, (uint64_t)M, Cc);
     }
-    float* t = cur;
-    cur = nxt;
-    nxt = t;
+    float* t = a;
+    a = b;
+    b = t;
   }
-  *out = cur;
+  if (zero_other) PL_CUDA(cudaMemsetAsync(b, 0, sizeof(float) * (size_t)M * Cc, st));
+  *out = a;
   return PL_OK;
 }
 

@@ -156,6 +156,210 @@ tile_build_kernel(const int32_t* __restrict__ vid, const float* __restrict__ bar
   }
 }
 
+// ---------------------------------------------------------------------------
+// tile build without a sort (TE <= 1024, i.e. d <= 7): one CTA per tile
+//   1. distinct vertices of the tile via a small open-addressing set in shared memory
+//   2. local index = rank of the occupied slot
+//   3. stable counting sort of the entries by local index: 32-entry chunks, in-chunk rank
+//      from match.any, per-(chunk, vertex) counts prefix-summed over the chunks
+// Entries of one vertex keep their (pixel, remainder) order, so the tile-internal
+// summation order of the splat stays fixed from run to run.
+// ---------------------------------------------------------------------------
+constexpr int kHashSlots = 2048;
+constexpr int kFastMaxTE = 1024;
+
+__global__ void __launch_bounds__(kThreads)
+tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict__ bary, int64_t n,
+                       int d1, uint8_t* __restrict__ ent_pix, float* __restrict__ ent_w,
+                       uint16_t* __restrict__ loc, int2* __restrict__ useg,
+                       int* __restrict__ tile_off, int* __restrict__ tile_U,
+                       int* __restrict__ counter, uint8_t* __restrict__ rec_slice,
+                       uint8_t* __restrict__ rec_splat) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned short* s_cnt = reinterpret_cast<unsigned short*>(smem_raw);  // [nchunks][TE]
+  __shared__ int h_key[kHashSlots];
+  __shared__ unsigned short h_lidx[kHashSlots];
+  __shared__ int s_uvid[kFastMaxTE];
+  __shared__ unsigned short s_start[kFastMaxTE], s_total[kFastMaxTE];
+  __shared__ int warp_cnt[kThreads / 32];
+  __shared__ int s_off;
+
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int TE = kTile * d1;
+  const int64_t tile = blockIdx.x;
+  const int64_t e0 = tile * TE;
+  const int64_t E = n * d1;
+  const int valid = (int)((E - e0) < TE ? (E - e0) : TE);
+  constexpr int QMAX = kFastMaxTE / kThreads;  // entries per thread
+  const int nq = (TE + kThreads - 1) / kThreads;
+
+  float* rs_bary = reinterpret_cast<float*>(rec_slice + tile * (int64_t)TE * 6);
+  uint16_t* rs_loc = reinterpret_cast<uint16_t*>(rs_bary + TE);
+  float* rp_w = reinterpret_cast<float*>(rec_splat + tile * (int64_t)TE * 9);
+  int32_t* rp_vid = reinterpret_cast<int32_t*>(rp_w + TE);
+  uint8_t* rp_pix = reinterpret_cast<uint8_t*>(rp_vid + TE);
+
+  for (int i = tid; i < kHashSlots; i += kThreads) h_key[i] = -1;
+  int my_vid[QMAX];
+  float my_w[QMAX];
+#pragma unroll
+  for (int q = 0; q < QMAX; q++) {
+    const int e = tid + q * kThreads;
+    my_vid[q] = (q < nq && e < valid) ? vid[e0 + e] : -1;
+    my_w[q] = (q < nq && e < valid) ? bary[e0 + e] : 0.f;
+  }
+  __syncthreads();
+
+  // 1. insert; remember the slot
+  int my_slot[QMAX];
+#pragma unroll
+  for (int q = 0; q < QMAX; q++) {
+    my_slot[q] = 0;
+    if (my_vid[q] >= 0) {
+      unsigned h = ((unsigned)my_vid[q] * 2654435761u) >> 21;  // top 11 bits
+      for (;;) {
+        const int old = atomicCAS(&h_key[h], -1, my_vid[q]);
+        if (old == -1 || old == my_vid[q]) break;
+        h = (h + 1) & (kHashSlots - 1);
+      }
+      my_slot[q] = (int)h;
+    }
+  }
+  __syncthreads();
+
+  // 2. local index = rank of the occupied slot (8 consecutive slots per thread)
+  int U;
+  {
+    constexpr int SPT = kHashSlots / kThreads;
+    int occ = 0;
+#pragma unroll
+    for (int k = 0; k < SPT; k++) occ += h_key[tid * SPT + k] >= 0 ? 1 : 0;
+    int incl = occ;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += y;
+    }
+    if (lane == 31) warp_cnt[wid] = incl;
+    __syncthreads();
+    int before = 0;
+    U = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; w++) {
+      const int c = warp_cnt[w];
+      before += (w < wid) ? c : 0;
+      U += c;
+    }
+    int u = before + incl - occ;
+#pragma unroll
+    for (int k = 0; k < SPT; k++) {
+      const int key = h_key[tid * SPT + k];
+      if (key >= 0) {
+        h_lidx[tid * SPT + k] = (unsigned short)u;
+        s_uvid[u] = key;
+        u++;
+      }
+    }
+  }
+  const int nchunks = (TE + 31) / 32;
+  for (int i = tid; i < nchunks * U; i += kThreads) s_cnt[(i / U) * TE + (i % U)] = 0;
+  __syncthreads();
+
+  // 3. in-chunk stable rank + per-(chunk, vertex) counts
+  int my_u[QMAX], my_r[QMAX];
+#pragma unroll
+  for (int q = 0; q < QMAX; q++) {
+    my_u[q] = 0xFFFF;
+    my_r[q] = 0;
+    if (q < nq) {  // uniform: whole warps take part in match.any
+      const int u = my_vid[q] >= 0 ? (int)h_lidx[my_slot[q]] : 0xFFFF;
+      const unsigned peers = __match_any_sync(0xffffffffu, u);
+      my_u[q] = u;
+      my_r[q] = __popc(peers & ((1u << lane) - 1u));
+      const int chunk = wid + q * (kThreads / 32);
+      if (u != 0xFFFF && my_r[q] == 0) s_cnt[chunk * TE + u] = (unsigned short)__popc(peers);
+    }
+  }
+  __syncthreads();
+  // prefix over the chunks, per vertex
+  for (int u = tid; u < U; u += kThreads) {
+    int running = 0;
+    for (int c = 0; c < nchunks; c++) {
+      const int t = s_cnt[c * TE + u];
+      s_cnt[c * TE + u] = (unsigned short)running;
+      running += t;
+    }
+    s_total[u] = (unsigned short)running;
+  }
+  __syncthreads();
+  // exclusive scan of the per-vertex totals (U <= 1024: 4 per thread)
+  {
+    int t[QMAX], sum = 0;
+#pragma unroll
+    for (int k = 0; k < QMAX; k++) {
+      const int u = tid * QMAX + k;
+      t[k] = u < U ? (int)s_total[u] : 0;
+      sum += t[k];
+    }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += y;
+    }
+    __syncthreads();  // warp_cnt reuse
+    if (lane == 31) warp_cnt[wid] = incl;
+    __syncthreads();
+    int before = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; w++) before += (w < wid) ? warp_cnt[w] : 0;
+    int run = before + incl - sum;
+#pragma unroll
+    for (int k = 0; k < QMAX; k++) {
+      const int u = tid * QMAX + k;
+      if (u < U) s_start[u] = (unsigned short)run;
+      run += t[k];
+    }
+  }
+  if (tid == 0) {
+    s_off = atomicAdd(counter, U);
+    tile_off[tile] = s_off;
+    tile_U[tile] = U;
+  }
+  __syncthreads();
+
+  // 4. scatter
+#pragma unroll
+  for (int q = 0; q < QMAX; q++) {
+    const int e = tid + q * kThreads;
+    if (q < nq && e < TE) {
+      if (my_vid[q] >= 0) {
+        const int u = my_u[q];
+        const int chunk = wid + q * (kThreads / 32);
+        const int pos = (int)s_start[u] + (int)s_cnt[chunk * TE + u] + my_r[q];
+        const uint8_t pix = (uint8_t)(e / d1);
+        ent_pix[e0 + pos] = pix;
+        ent_w[e0 + pos] = my_w[q];
+        loc[e0 + e] = (uint16_t)u;
+        rp_w[pos] = my_w[q];
+        rp_vid[pos] = my_vid[q];
+        rp_pix[pos] = pix;
+        rs_bary[e] = my_w[q];
+        rs_loc[e] = (uint16_t)u;
+      } else {  // pads of the last tile: weight 0, vertex 0
+        rp_w[e] = 0.f;
+        rp_vid[e] = 0;
+        rp_pix[e] = 0;
+        rs_bary[e] = 0.f;
+        rs_loc[e] = 0;
+      }
+    }
+  }
+  const int off = s_off;
+  for (int u = tid; u < U; u += kThreads)
+    useg[off + u] = make_int2(s_uvid[u], (int)s_start[u] | ((int)s_total[u] << 16));
+}
+
 int pow2_ceil_i(int x) {
   int p = 1;
   while (p < x) p <<= 1;
@@ -183,6 +387,16 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   PL_TRY(dev_alloc((void**)&L->rec_splat, E_pad * 9, st));
   L->bytes += (int64_t)(E_pad * (1 + 4 + 2 + 8 + 6 + 9) + sizeof(int) * (size_t)(2 * ntiles + 1));
   PL_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), st));
+  if (TE <= kFastMaxTE) {
+    const size_t smem = sizeof(unsigned short) * (size_t)((TE + 31) / 32) * TE;
+    // static (20.5 KB) + dynamic shared memory exceeds the 48 KB default: always opt in
+    PL_CUDA(cudaFuncSetAttribute(tile_build_fast_kernel,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    PL_LAUNCH(tile_build_fast_kernel, (unsigned)ntiles, kThreads, smem, st, L->vid, L->bary, L->n,
+              d1, L->ent_pix, L->ent_w, L->loc, L->useg, L->tile_off, L->tile_U, counter,
+              L->rec_slice, L->rec_splat);
+    return PL_OK;
+  }
   const size_t smem = sizeof(unsigned long long) * NS + sizeof(unsigned short) * (TE + 2);
   if (smem > 48 * 1024)
     PL_CUDA(cudaFuncSetAttribute(tile_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

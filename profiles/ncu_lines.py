@@ -1,6 +1,6 @@
 """Summarise an ncu report: key raw metrics + the source lines with most stall samples.
 
-    python profiles/ncu_lines.py gpurun_out/x.ncu-rep [top_n]
+    python profiles/ncu_lines.py gpurun_out/x.ncu-rep [top_n] [kernel_index]
 """
 import csv
 import io
@@ -26,6 +26,7 @@ def run(args):
 def main():
     rep = sys.argv[1]
     top = int(sys.argv[2]) if len(sys.argv) > 2 else 25
+    which = int(sys.argv[3]) if len(sys.argv) > 3 else 0
     rows = list(csv.reader(io.StringIO(run(["-i", rep, "--page", "raw", "--csv"]))))
     hdr, units = rows[0], rows[1]
     print("Kernel:", [r[hdr.index("Kernel Name")] for r in rows[2:]])
@@ -37,13 +38,13 @@ def main():
     his = [i for i, r in enumerate(rows) if r and r[0] == "Line No"]
     if not his:
         return
-    hi = his[0]
+    hi = his[min(which, len(his) - 1)]
     hdr = rows[hi]
-    end = his[1] if len(his) > 1 else len(rows)
+    end = ([h for h in his if h > hi] + [len(rows)])[0]
     samp, inst = hdr.index("# Samples"), hdr.index("Instructions Executed")
     lines = [r for r in rows[hi + 1:end] if r and r[0].isdigit()]
     tot = sum(int(r[samp]) for r in lines if r[samp].isdigit())
-    print("total samples (first kernel):", tot)
+    print(f"total samples (kernel #{which}):", tot)
     stall_cols = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
     lines.sort(key=lambda r: -int(r[samp]) if r[samp].isdigit() else 0)
     for r in lines[:top]:
