@@ -59,68 +59,96 @@ def _inputs(seed):
 
 
 class _ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region, polled through NVML from a thread
+    (the timed region lasts tens of milliseconds: `nvidia-smi -lms` is too coarse for it)."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index):
-        self.gpu, self.proc, self.path = gpu_index, None, None
+        self.gpu, self.thread, self.stop_flag = gpu_index, None, False
+        self.sm, self.bits, self.max_mhz, self.power = [], 0, None, []
 
-    def start(self):
+    def _run(self):
         try:
-            fd, self.path = tempfile.mkstemp(suffix=".csv")
-            os.close(fd)
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
-        except Exception:
-            self.proc = None
-
-    def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, reasons = [], set()
-        try:
-            for line in open(self.path):
-                f = [x.strip() for x in line.split(",")]
-                if len(f) < 9:
-                    continue
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.gpu
+            if vis:
                 try:
-                    sm.append(float(f[1]))
-                    out["sm_max_mhz"] = float(f[2])
-                except ValueError:
-                    continue
-                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
-                                      "sw_power_cap"), f[5:9]):
-                    if val.lower().startswith("active"):
-                        reasons.add(name)
-            os.unlink(self.path)
+                    idx = int(vis.split(",")[self.gpu])
+                except Exception:
+                    idx = self.gpu
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            while not self.stop_flag:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                try:
+                    self.bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    try:
+                        self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                    except Exception:
+                        pass
+                try:
+                    self.power.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
+                except Exception:
+                    pass
+                time.sleep(0.002)
         except Exception:
             pass
-        if sm:
-            out["sm_mhz"] = statistics.median(sm)
-        out["reasons"] = sorted(reasons)
+
+    def start(self):
+        import threading
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.thread is not None:
+            self.thread.join(timeout=5)
+        out = {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": len(self.sm)}
+        if self.sm:
+            out["sm_mhz"] = statistics.median(self.sm)
+        if self.power:
+            out["power_w_max"] = max(self.power)
+        out["reasons"] = sorted(name for bit, name in self.REASONS.items() if self.bits & bit)
         return out
 
 
-def _algorithmic_bytes(kernel, n, M, C):
-    """Per-launch algorithmic HBM bytes (DESIGN.md 'kernels'); d = 5, fp32."""
+def _algorithmic_bytes(kernel, n, M, C, launches_per_frame=None):
+    """Per-launch algorithmic HBM bytes; d = 5, fp32."""
     d1 = D + 1
-    if kernel.startswith("splat_kernel"):      # read src + replay, write lattice values
-        return 4 * n * C + 8 * n * d1 + 4 * M * C
+    if kernel.startswith("mf_tc_kernel") or kernel.startswith("mf_fused_kernel"):
+        # fused iteration: first launch of a frame reads E0, writes P (+ splat record, lattice
+        # rows written); the others also read P_prev, the slice record and the blurred lattice.
+        first = 8 * n * C + 9 * n * d1 + 4 * M * C
+        later = 12 * n * C + 15 * n * d1 + 8 * M * C
+        k = NITERS if launches_per_frame is None else int(round(launches_per_frame))
+        return (first + (k - 1) * later) / k
+    if kernel.startswith("splat"):             # read src + entry lists, write lattice values
+        return 4 * n * C + 9 * n * d1 + 4 * M * C
     if kernel.startswith("blur_kernel"):       # one axis: read + write values, neighbour ids
         return 8 * M * C + 8 * M
-    if kernel.startswith("slice_kernel"):      # read values + replay + P + E0, write E
-        return 4 * M * C + 8 * n * d1 + 12 * n * C
+    if kernel.startswith("blur_"):             # all d+1 axes in one launch
+        return d1 * (8 * M * C + 8 * M)
+    if kernel.startswith("slice"):             # read values + entry lists + P + E0, write E
+        return 4 * M * C + 6 * n * d1 + 12 * n * C
     if kernel.startswith("softmax_compat"):    # read E, write P, Mu once
         return 8 * n * C + 4 * C * C
+    return None
+
+
+def _ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, taken from the
+    committed ncu --set full summary (profiles/ncu_traffic.json); None if not captured."""
+    try:
+        tab = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        for key, val in tab.items():
+            if kernel.startswith(key):
+                return val["dram_bytes_per_launch"]
+    except Exception:
+        pass
     return None
 
 
@@ -281,9 +309,9 @@ def run_ours(args, rank, local_rank, world):
             depth = mb.logits2average_depth(crf(g, lg))
             depth_h.copy_(depth, non_blocking=True)
             torch.cuda.synchronize(dev)
-        pkg.crf.gaussian_matrix.clear_lattice_cache()
+        gm.clear_lattice_cache()
 
-    importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
+    gm = importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
     for _ in range(args.warmup):
         e2e_step()
     barrier()
@@ -291,8 +319,60 @@ def run_ours(args, rank, local_rank, world):
     for _ in range(args.steps):
         e2e_step()
     barrier()
+    e2e_serial_s = reduce_max(time.perf_counter() - t0)
+    e2e_serial = world * args.steps / e2e_serial_s
+
+    # Same work with two frames in flight: two host threads, each with its own copy / compute
+    # streams and device buffers, take alternate frames, so the H2D copy of one frame overlaps
+    # the CRF of the other (the module call blocks its thread while the lattice's vertex count
+    # comes back).  Every frame's H2D and D2H is inside the timed region.
+    import threading
+    NT = 2
+    streams = [(torch.cuda.Stream(dev), torch.cuda.Stream(dev)) for _ in range(NT)]
+    g_d = [torch.empty_like(guide_h, device=dev) for _ in range(NT)]
+    lg_d = [torch.empty_like(logits_h, device=dev) for _ in range(NT)]
+    dh = [torch.empty((1, 1, H, W), dtype=torch.float32).pin_memory() for _ in range(NT)]
+
+    def worker(t, frames, errors):
+        try:
+            torch.cuda.set_device(dev)
+            copy_st, comp_st = streams[t]
+            ev = torch.cuda.Event()
+            with torch.no_grad():
+                for _ in range(frames):
+                    with torch.cuda.stream(copy_st):
+                        g_d[t].copy_(guide_h, non_blocking=True)
+                        lg_d[t].copy_(logits_h, non_blocking=True)
+                        ev.record(copy_st)
+                    ev.synchronize()               # inputs are on the device
+                    with torch.cuda.stream(comp_st):
+                        depth = mb.logits2average_depth(crf(g_d[t], lg_d[t]))
+                        dh[t].copy_(depth, non_blocking=True)
+                    comp_st.synchronize()          # this frame's depth map is on the host
+                    gm.forget(g_d[t])
+        except Exception as exc:                   # surface worker failures in the main thread
+            errors.append(exc)
+
+    def e2e_pipelined(steps):
+        errors = []
+        share = [steps // NT + (1 if t < steps % NT else 0) for t in range(NT)]
+        threads = [threading.Thread(target=worker, args=(t, share[t], errors)) for t in range(NT)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        torch.cuda.synchronize(dev)
+        if errors:
+            raise errors[0]
+
+    e2e_pipelined(max(args.warmup, 6 * NT))   # both threads past their first-touch allocations
+    barrier()
+    t0 = time.perf_counter()
+    e2e_pipelined(args.steps)
+    barrier()
     e2e_s = reduce_max(time.perf_counter() - t0)
     e2e_value = world * args.steps / e2e_s
+    gm.clear_lattice_cache()
 
     # ---- per-kernel durations for the roofline (separate pass, same inputs) ----
     roofline = None
@@ -308,14 +388,14 @@ def run_ours(args, rank, local_rank, world):
         M = state["M"]
         top = max(rep.items(), key=lambda kv: kv[1][1])
         name, (cnt, ms) = top
-        nbytes = _algorithmic_bytes(name, n, M, L)
+        nbytes = _algorithmic_bytes(name, n, M, L, cnt / 3)
         frame_ms = sum(v[1] for v in rep.values()) / 3
         kernels = {k: {"launches_per_frame": v[0] / 3, "ms_per_frame": v[1] / 3,
                        "share": v[1] / 3 / frame_ms} for k, v in rep.items()}
         if nbytes is not None:
             achieved = nbytes / (ms / cnt * 1e-3) / 1e9
             roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak,
-                        "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                        "unit": "GB/s", "frac": achieved / peak, "traffic": _ncu_traffic(name),
                         "peak_source": how, "avg_launch_us": ms / cnt * 1e3,
                         "algorithmic_bytes_per_launch": nbytes, "vertices": M, "kernels": kernels}
         else:
@@ -344,7 +424,9 @@ def run_ours(args, rank, local_rank, world):
                        "step": "lattice build + 5 fused mean-field iterations, inputs in HBM"},
             "e2e": {"value": e2e_value, "unit": "frames/s",
                     "h2d_bytes_per_step": int(guide_h.numel() + logits_h.numel()) * 4,
-                    "d2h_bytes_per_step": int(depth_h.numel()) * 4},
+                    "d2h_bytes_per_step": int(depth_h.numel()) * 4,
+                    "mode": "two frames in flight (two host threads, own streams): H2D of one overlaps the CRF of the other",
+                    "serial_value": e2e_serial},
             "gpu_launches": int(launches) * world,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "extra": {"lattice_filter_mpix_labels_per_s_incl_build": n * L * NITERS / (ms_per_step * 1e-3) / 1e6,
@@ -357,7 +439,7 @@ def run_ours(args, rank, local_rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")

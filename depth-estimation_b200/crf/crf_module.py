@@ -79,7 +79,8 @@ class charb(nn.Module):
 
     def matrix(self, L, labels=None, device=None):
         if labels is None:
-            labels = torch.arange(L).float().to(device if device is not None else self.gamma.device)
+            labels = torch.arange(L, dtype=torch.float32,
+                                  device=device if device is not None else self.gamma.device)
         labels = labels.reshape(-1)
         return charbonneir(labels[None, :], labels[:, None], self.gamma)
 
@@ -128,13 +129,26 @@ class CRFasRNN(nn.Module):
             Q = F.softmax(-E, dim=1)
         return -E
 
+    def _compat_cached(self, L, labels, dev):
+        """(Mu matrix on the device, exp(s) as a host float), recomputed only when gamma / s /
+        labels change -- reading exp(s) back costs a host-device synchronisation per call."""
+        key = (L, str(dev), self.Mu.gamma._version, self.Mu.s._version,
+               self.Mu.gamma.data_ptr(), self.Mu.s.data_ptr(),
+               None if labels is None else (labels.data_ptr(), labels._version, tuple(labels.shape)))
+        hit = getattr(self, "_compat_cache", None)
+        if hit is None or hit[0] != key:
+            mu = self.Mu.matrix(L, labels, dev).float().contiguous()
+            scale = float(torch.exp(self.Mu.s))
+            hit = (key, mu, scale)
+            self._compat_cache = hit
+        return hit[1], hit[2]
+
     def _forward_fused(self, refs, E0, labels):
         B, L, H, W = E0.shape
         n, d = H * W, refs.shape[1]
         dev = E0.device
         with torch.no_grad():
-            mu = self.Mu.matrix(L, labels, dev).float().contiguous()
-            scale = float(torch.exp(self.Mu.s))
+            mu, scale = self._compat_cached(L, labels, dev)
             flat_refs = _cached(
                 refs, lambda: refs.reshape(B, d, -1).permute(0, 2, 1).contiguous())
             E0c = E0.float().contiguous()

@@ -57,6 +57,29 @@ def lattice_for(ref):
     return _cached(ref, lambda: PermutohedralLattice(ref.detach()))
 
 
+def set_lattice_cache_limit(entries):
+    """Bound the cache (oldest entries are destroyed first).  A frame holds two entries (the
+    flattened guide and its lattice); a streaming caller that keeps k frames in flight wants
+    2k so device memory is returned to the pool as it goes."""
+    global _CACHE_MAX
+    _CACHE_MAX = max(2, int(entries))
+
+
+def forget(guide_imgs):
+    """Drop (and free) what the cache holds for one guide batch ``[B, d, h, w]``: its flattened
+    copy and the lattices built from it.  For streaming callers: call once the frame's work
+    has completed on the device."""
+    hit = _CACHE.pop(_key(guide_imgs), None)
+    if hit is None:
+        return
+    flat_refs = hit[1]
+    if isinstance(flat_refs, torch.Tensor) and flat_refs.dim() == 3:
+        for b in range(flat_refs.shape[0]):
+            lat = _CACHE.pop(_key(flat_refs[b]), None)
+            if lat is not None and isinstance(lat[1], PermutohedralLattice):
+                lat[1].close()
+
+
 def clear_lattice_cache():
     while _CACHE:
         old = _CACHE.popitem()[1][1]

@@ -17,7 +17,10 @@ def logits2average_depth(logits, labels=None):
     """mb_stereo_crf.py:62-66: soft-argmax depth."""
     probs = F.softmax(logits, dim=1)
     if labels is None:
-        labels = torch.arange(probs.shape[1]).float().to(probs.device)[None, :, None, None]
+        # created on the device: the reference's host arange + .to(device) is a pageable H2D
+        # copy, which blocks the calling thread until the stream has drained
+        labels = torch.arange(probs.shape[1], dtype=torch.float32,
+                              device=probs.device)[None, :, None, None]
     average_depths = (probs * labels).sum(1)
     return average_depths[:, None, :, :]
 
