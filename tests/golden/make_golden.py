@@ -1,0 +1,191 @@
+"""Generate the golden vectors in tests/golden/ by running the REAL reference Python modules.
+
+TEST INFRASTRUCTURE.  Runs only where /root/reference exists (this container); the vectors it
+writes (small .npz files, committed) travel to the GPU box.
+
+    python tests/golden/make_golden.py
+
+The reference's crf/gaussian_matrix.py cannot be imported as it stands:
+  * line 8 imports the un-vendored `guided_filter_pytorch`      -> stub module (classes unused here)
+  * line 15 JIT-builds ~/depth-estimation/crf/lattice/lite/lattice.cpp, which no longer compiles
+    against torch 2.11 (tensorFromBlob)                          -> torch.utils.cpp_extension.load is
+    patched to return a module whose `filter` is oracle/_ref/libref_lattice.so, i.e. the
+    unmodified reference header permutohedral.h compiled in place (oracle/build_ref.py).
+Everything else -- LatticeFilter / BatchedLatticeFilter forward and backward, BatchedAdjacency,
+LatticeGaussian, RbfLaplacian(C), charb, potts, compatibility_matrix, mean_field_infer,
+CRFasRNN.forward, ijrgbGuide, ijGuide -- is the reference's own code, executed on CPU.
+`crf/mb_stereo_crf.py` needs the un-vendored `oil` package at import; `oil`, the data loader and
+matplotlib are stubbed so that its nn.Module forwards (logits2average_depth, CRFdepthRefiner) run.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = "/root/reference"
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    m.__dict__.update(attrs)
+    sys.modules[name] = m
+    return m
+
+
+def import_reference():
+    from oracle.lattice_oracle import Reference
+    ref = Reference()
+
+    def ref_filter(src, refm):
+        out = ref.filter(src.detach().contiguous().numpy(), refm.detach().contiguous().numpy())
+        return torch.from_numpy(out)
+
+    class _Dummy(torch.nn.Module):
+        def __init__(self, *a, **k):
+            super().__init__()
+
+    gfp = _stub("guided_filter_pytorch")
+    gfp.guided_filter = _stub("guided_filter_pytorch.guided_filter", GuidedFilter=_Dummy,
+                              BoxFilter=_Dummy)
+    import torch.utils.cpp_extension as ce
+    ce.load = lambda *a, **k: types.SimpleNamespace(filter=ref_filter)
+
+    # stubs for crf/mb_stereo_crf.py's imports (oil, data loader, plotting)
+    class _Trainer:
+        def __init__(self, *a, **k):
+            pass
+    oil = _stub("oil")
+    oil.utils = _stub("oil.utils")
+    _stub("oil.utils.utils", Eval=None, cosLr=None, LoaderTo=None, Named=type)
+    _stub("oil.model_trainers", Trainer=_Trainer, Classifier=_Trainer, Regressor=_Trainer)
+    _stub("oil.utils.mytqdm", tqdm=lambda x, **k: x)
+    _stub("oil.architectures")
+    _stub("oil.architectures.parts")
+    _stub("oil.architectures.parts.blocks", conv2d=None, ConvBNrelu=None, ResBlock=None)
+    _stub("crf.dataloader", MBStereo14Unary=None, StereoUpsampling05=None)
+    if "matplotlib" not in sys.modules:
+        try:
+            import matplotlib  # noqa: F401
+        except Exception:
+            mpl = _stub("matplotlib")
+            mpl.pyplot = _stub("matplotlib.pyplot")
+
+    sys.path.insert(0, REF)
+    import crf.gaussian_matrix as rgm
+    import crf.crf_module as rcm
+    # the reference fans the batch out over mp.Pool (gaussian_matrix.py:370-377); same filter,
+    # run in-process here
+    rgm.batched_filter = lambda srcs, refs, nt: torch.stack(
+        [rgm.latticefilter(s.contiguous(), r.contiguous()) for s, r in zip(srcs, refs)])
+    try:
+        import crf.mb_stereo_crf as rmb
+    except Exception as exc:  # pragma: no cover - informational
+        print("crf.mb_stereo_crf not importable:", exc)
+        rmb = None
+    return ref, rgm, rcm, rmb
+
+
+def main():
+    synthetic = __import__("importlib").import_module("depth_estimation_b200.synthetic")
+    ref, rgm, rcm, rmb = import_reference()
+    torch.manual_seed(0)
+    out = {}
+
+    # ---- 1. lattice integer artefacts + filter on an (r,g,b,i,j)-ordered guide -------------
+    h, w = 24, 32
+    img = synthetic.image(h, w, seed=5)
+    feats = synthetic.ijrgb_features(img, 0.05, 0.125, rgb_first=True)   # gaussian_matrix.py:498-505
+    st = ref.state(feats)
+    src = np.random.default_rng(1).random((h * w, 7)).astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "lattice_state_24x32.npz"), ref=feats, src=src,
+                        greedy=st.greedy, rank=st.rank, bary=st.bary, vid=st.vid, keys=st.keys,
+                        nbr=st.nbr, M=np.int64(st.M), filtered=ref.filter(src, feats))
+
+    # ---- 2. LatticeFilter forward / backward (gaussian_matrix.py:423-468) ------------------
+    g = torch.Generator().manual_seed(2)
+    n, L, d = 300, 3, 3
+    s = torch.rand((n, L), generator=g).requires_grad_()
+    r = (torch.rand((n, d), generator=g) * 3).requires_grad_()
+    gout = torch.randn((n, L), generator=g)
+    y = rgm.LatticeFilter.apply(s, r)
+    y.backward(gout)
+    np.savez_compressed(os.path.join(HERE, "lattice_filter_autograd.npz"), src=s.detach().numpy(),
+                        ref=r.detach().numpy(), gout=gout.numpy(), out=y.detach().numpy(),
+                        grad_src=s.grad.numpy(), grad_ref=r.grad.numpy())
+
+    # ---- 3. operators on one lattice: LatticeGaussian, RbfLaplacian(C) (:292-338) ----------
+    # guide scales 0.2: every point has neighbours (degree K1 - 1 >= 2), so the normalised
+    # Laplacians are well conditioned (with 0.1 some degrees are ~0 or negative: 'sym' is NaN)
+    refm = torch.from_numpy(synthetic.ijrgb_features(synthetic.image(20, 28, seed=7), 0.2, 0.2))
+    U = torch.rand((refm.shape[0], 2), generator=g)
+    ops = {"gaussian": rgm.LatticeGaussian(refm) @ U,
+           "lap_norm": rgm.RbfLaplacian(refm, normalize=True) @ U,
+           "lap_unnorm": rgm.RbfLaplacian(refm, normalize=False) @ U,
+           "lapc_sym": rgm.RbfLaplacianC(refm, 'sym') @ U,
+           "lapc_right": rgm.RbfLaplacianC(refm, 'right') @ U,
+           "lapc_none": rgm.RbfLaplacianC(refm, None) @ U}
+    np.savez_compressed(os.path.join(HERE, "lattice_operators.npz"), ref=refm.numpy(), U=U.numpy(),
+                        **{k: v.detach().numpy() for k, v in ops.items()})
+
+    # ---- 4. CRFasRNN forward + backward with W = BatchedAdjacency (crf_module.py:81-104) ----
+    h, w, L, niters = 20, 28, 8, 3
+    img = synthetic.image(h, w, seed=9)
+    rgb = torch.from_numpy(img).permute(2, 0, 1)[None].contiguous()
+    logits = (-torch.from_numpy(synthetic.unary(h, w, L, 9)).reshape(h, w, L)).permute(2, 0, 1)[None]
+    logits = logits.contiguous().requires_grad_()
+    guide_mod = rcm.ijrgbGuide(0.1, 0.1)
+    crf = rcm.CRFasRNN(rcm.charb(0.05), niters=niters)
+    crf.W = rgm.BatchedAdjacency(num_threads=1)     # the lattice pairwise (imported at crf_module.py:5)
+    labels = torch.arange(L).float()                 # charb's default is .cuda() (crf_module.py:73)
+    conf = torch.rand((1, 1, h, w), generator=g) * 0.5 + 0.75
+    guide = guide_mod(rgb)
+    out_logits = crf(guide, logits, confidence=conf, labels=labels)
+    target = torch.from_numpy(synthetic.disparity(h, w, L, 9)).float()[None, None]
+    probs = torch.softmax(out_logits, dim=1)
+    depth = (probs * labels[None, :, None, None]).sum(1)[:, None]
+    loss = (depth - target).abs().mean()
+    loss.backward()
+    np.savez_compressed(os.path.join(HERE, "crf_as_rnn_20x28.npz"), rgb=rgb.numpy(),
+                        logits=logits.detach().numpy(), confidence=conf.numpy(),
+                        guide=guide.detach().numpy(), out_logits=out_logits.detach().numpy(),
+                        depth=depth.detach().numpy(), loss=np.float32(loss.item()),
+                        target=target.numpy(), grad_logits=logits.grad.numpy(),
+                        grad_gamma=crf.Mu.gamma.grad.numpy(), grad_s=crf.Mu.s.grad.numpy(),
+                        grad_s_ij=guide_mod.s_ij.grad.numpy(), grad_s_rgb=guide_mod.s_rgb.grad.numpy(),
+                        niters=np.int64(niters), gamma=np.float32(0.05))
+
+    # ---- 5. matrix form: mean_field_infer, compatibility_matrix, potts, charb energies -----
+    n, L = refm.shape[0], 6
+    E0 = torch.rand((n, L), generator=g) * 4
+    lab = torch.linspace(0, 3, L)
+    Mu = rcm.compatibility_matrix(rcm.charbonneir, lab)
+    Q = rcm.mean_field_infer(E0, rgm.LatticeGaussian(refm), Mu, niters=4)
+    pt = rcm.potts(5)
+    x = torch.rand((1, 5, 6, 7), generator=g)
+    ch = rcm.charb(0.05)
+    disp = torch.rand((1, 1, 6, 7), generator=g) * 3
+    en = ch.get_energies_from_scalar(disp, lab[None, :, None, None])
+    np.savez_compressed(os.path.join(HERE, "crf_matrix_form.npz"), ref=refm.numpy(), E0=E0.numpy(),
+                        labels=lab.numpy(), Mu=Mu.numpy(), Q=Q.detach().numpy(), potts_x=x.numpy(),
+                        potts_y=pt(x).detach().numpy(), disp=disp.numpy(),
+                        energies=en.detach().numpy(),
+                        Mu2=rcm.compatibility_matrix(rcm.charbonneir2, lab).numpy(),
+                        ij_guide=rcm.ijGuide(0.2)(x).detach().numpy())
+
+    # ---- 6. stereo wrappers (mb_stereo_crf.py:62-79) ---------------------------------------
+    if rmb is not None:
+        lg = torch.randn((2, 5, 6, 7), generator=g)
+        np.savez_compressed(os.path.join(HERE, "stereo_wrappers.npz"), logits=lg.numpy(),
+                            depth=rmb.logits2average_depth(lg).numpy(),
+                            depth_labels=rmb.logits2average_depth(
+                                lg, torch.linspace(0, 2, 5)[None, :, None, None]).numpy())
+    print("golden vectors written to", HERE)
+
+
+if __name__ == "__main__":
+    main()
