@@ -45,6 +45,8 @@ _SIGNATURES = {
                                     C.c_int, C.c_float, C.c_void_p]),
     "pl_softmax_compat_ex": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                        C.c_int, C.c_float, C.c_uint32, C.c_void_p]),
+    "pl_softmax_compat_blocked": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64,
+                                            C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
     "pl_meanfield": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                C.c_int, C.c_float, C.c_uint32, C.c_void_p]),
     "pl_nchw_to_nlc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_float,

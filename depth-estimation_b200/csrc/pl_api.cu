@@ -239,6 +239,9 @@ int pl_filter_host(const float* src_host, const float* ref_host, float* dst_host
   return r;
 }
 
+static int compat_large(const float* e, int nblocks, const float* muT, float* p, float* q_out,
+                        int64_t n, int L, int l0, int N, float scale, cudaStream_t st);
+
 int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
                          int64_t n, int L, float scale, uint32_t flags, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
@@ -254,7 +257,38 @@ int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev,
     pl::dev_free(mu_canon, st);
     return r;
   }
+  if (!(flags & PL_MEANFIELD_NO_TENSOR) && aligned && e_dev && muT_dev && p_dev && n > 0 &&
+      L > 64 && L <= 256 && pl::compat_tc_supported(L, L, L)) {
+    PL_TRY(pl::check_device());
+    return compat_large(e_dev, 1, muT_dev, p_dev, q_out_dev, n, L, 0, L, scale, st);
+  }
   return pl::softmax_compat(e_dev, muT_dev, p_dev, q_out_dev, n, L, scale, st);
+}
+
+static int compat_large(const float* e, int nblocks, const float* muT, float* p, float* q_out,
+                        int64_t n, int L, int l0, int N, float scale, cudaStream_t st) {
+  uint8_t* rec = nullptr;
+  PL_TRY(pl::dev_alloc((void**)&rec, pl::compat_tc_mu_bytes(L, N), st));
+  int r = pl::compat_tc_prepare_mu(muT, L, l0, N, rec, st);
+  if (r == PL_OK) r = pl::compat_tc_run(e, nblocks, L / nblocks, rec, p, q_out, n, L, N, scale, st);
+  pl::dev_free(rec, st);
+  return r;
+}
+
+int pl_softmax_compat_blocked(const float* e_blocks_dev, int nblocks, const float* muT_dev,
+                              float* p_dev, int64_t n, int L, int l0, int N, float scale,
+                              void* stream) {
+  if (e_blocks_dev == nullptr || muT_dev == nullptr || p_dev == nullptr || n <= 0 || nblocks < 1 ||
+      L <= 0 || L % nblocks != 0 || l0 < 0 || N <= 0 || l0 + N > L ||
+      (((uintptr_t)e_blocks_dev | (uintptr_t)p_dev) & 15u) != 0 ||
+      !pl::compat_tc_supported(L, N, L / nblocks)) {
+    pl::set_last_error("pl_softmax_compat_blocked: unsupported arguments (L=%d, N=%d, nblocks=%d)", L,
+                       N, nblocks);
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  return compat_large(e_blocks_dev, nblocks, muT_dev, p_dev, nullptr, n, L, l0, N, scale,
+                      (cudaStream_t)stream);
 }
 
 int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
@@ -316,8 +350,8 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
   }
   for (int it = 0; it < niters; it++) {
     // P = scale * Mu softmax(-E)          crf_module.py:99-100,102 with :71-75
-    PL_TRY(pl::softmax_compat(it == 0 ? e0_dev : e_out_dev, muT_dev, work_dev, nullptr, n, L,
-                              scale, st));
+    PL_TRY(pl_softmax_compat_ex(it == 0 ? e0_dev : e_out_dev, muT_dev, work_dev, nullptr, n, L,
+                                scale, flags & PL_MEANFIELD_NO_TENSOR, stream));
     // E = E0 + (filter(P) - P)            crf_module.py:101 with gaussian_matrix.py:350-352
     PL_TRY(pl::lattice_apply(Lt, work_dev, L, e_out_dev, L, L, work_dev, L, e0_dev, L, flags, st));
   }
@@ -373,7 +407,7 @@ int pl_profile_report(char* buf, int cap) {
 }
 
 uint64_t pl_launch_count(void) { return pl::g_launches; }
-int pl_debug_tc_timeouts(void) { return pl::tc_timeouts(); }
+int pl_debug_tc_timeouts(void) { return pl::tc_timeouts() + pl::ctc_timeouts(); }
 int pl_version(void) { return PL_VERSION; }
 
 const char* pl_error_string(int code) {

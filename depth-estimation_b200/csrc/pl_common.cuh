@@ -122,6 +122,13 @@ int mf_tc_iteration(Lattice* L, bool first, const float* val_in, float* val_out,
 int softmax_compat_tc(const float* e, const float* mu_canon, float* p, float* q_out, int64_t n,
                       int labels, float scale, cudaStream_t st);
 int tc_timeouts();
+// softmax + compatibility for large label counts / label shards on tcgen05 (pl_compat_tc.cu)
+bool compat_tc_supported(int L, int N, int block_w);
+size_t compat_tc_mu_bytes(int L, int N);
+int compat_tc_prepare_mu(const float* muT, int L, int l0, int N, uint8_t* mu_rec, cudaStream_t st);
+int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_rec, float* p,
+                  float* q_out, int64_t n, int L, int N, float scale, cudaStream_t st);
+int ctc_timeouts();
 // mean field (pl_meanfield.cu)
 int softmax_compat(const float* e, const float* muT, float* p, float* q_out, int64_t n, int L,
                    float scale, cudaStream_t st);

@@ -1,0 +1,333 @@
+// pl_compat_tc.cu -- softmax + label-compatibility transform for LARGE label counts on the
+// tcgen05 tensor cores (sm_100a):  P[p][j] = scale * sum_k Mu[l0 + j][k] * softmax_k(-E[p][.])
+// for j < N output labels (N = L on one GPU, N = L / G when the labels are sharded over G ranks).
+//
+// crf/crf_module.py:99-102 with charb.forward (:71-75), pixel-major.  L is a multiple of 64
+// (128, 256, ...), N a multiple of BN (32 or 64), N <= 256 (TMEM accumulator columns).
+//
+// Per tile of 128 pixels (= UMMA M), persistent CTAs:
+//   pass 1  online softmax statistics (row max, row sum) over all L labels, E from HBM
+//   pass 2  for every 64-wide K chunk: re-read the E chunk (L2), Q = exp(-E - max) / sum,
+//           split Q = hi + lo (tf32) into the canonical K-major operand planes A, then for every
+//           BN-wide block of output labels three MMAs (lo*hi + hi*lo + hi*hi, fp32 parity, see
+//           pl_fused_tc.cu) accumulate into that block's TMEM columns.  The Mu blocks (pre-split
+//           hi / lo planes, one contiguous record per (K chunk, N block)) stream through a
+//           two-deep TMA ring.
+//   epilogue TMEM -> registers -> shared memory -> coalesced rows of P
+//
+// E may be given in the BLOCKED layout an all-gather over label shards produces:
+// e[b][p][lw] with b < nblocks, lw < block_w, label = b * block_w + lw  (nblocks = 1: plain [n][L]).
+#include <math.h>
+
+#include "pl_common.cuh"
+#include "pl_tc.cuh"
+
+namespace pl {
+
+namespace {
+
+constexpr int kTile = PL_TILE;  // 128
+constexpr int kThreads = 256;
+constexpr int kKC = 64;                          // K chunk (labels per A / B record)
+constexpr int kA_CH = kTile * 16 + 16;           // bytes per 16-byte K chunk column of A
+constexpr int kA_BYTES = (kKC / 4) * kA_CH;      // one plane of A: 33024
+constexpr int kPLD = 64 + 4;                     // epilogue staging pitch (floats)
+
+__device__ int g_ctc_timeouts = 0;
+
+template <int BN>
+struct BCfg {
+  static constexpr int B_CH = BN * 16 + 16;
+  static constexpr int B_BYTES = (kKC / 4) * B_CH;   // one plane
+  static constexpr int REC = 2 * B_BYTES;            // hi | lo
+};
+
+struct CArgs {
+  const float* e;       // blocked [nblocks][n][block_w]
+  int nblocks, block_w;
+  const uint8_t* mu_rec;  // [(L/64)][N/BN] records of BCfg<BN>::REC bytes
+  float* p;             // [n][N]
+  float* q_out;         // [n][L] plain layout, or null
+  int64_t n, ntiles;
+  int L, N;
+  float scale;
+};
+
+__device__ __forceinline__ const float* e_ptr(const CArgs& a, int64_t p, int label) {
+  const int b = label / a.block_w;
+  return a.e + ((int64_t)b * a.n + p) * a.block_w + (label - b * a.block_w);
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
+  using B = BCfg<BN>;
+  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned char* s_a = smem;                       // A hi | lo planes; epilogue staging
+  unsigned char* s_b = smem + 2 * kA_BYTES;        // two B records (ring)
+  float* s_m = reinterpret_cast<float*>(s_b + 2 * B::REC);   // [128] row max of -E
+  float* s_inv = s_m + kTile;                                // [128] 1 / row sum
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + kTile);
+  // bars: [0,1] B record landed (ring slot)  [2,3] ring slot free  [4] all MMAs on A done
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = tid >> 4, l = tid & 15;   // 16 lanes per pixel row, 16 rows per pass
+  constexpr int RPT = kTile / 16;         // 8 rows per thread
+  const int KCH = a.L / kKC;              // K chunks
+  const int NB = a.N / BN;                // output blocks
+  const int steps_per_tile = KCH * NB;
+  const uint32_t tmem_cols = a.N <= 32 ? 32 : (a.N <= 64 ? 64 : (a.N <= 128 ? 128 : 256));
+
+  if (warp == 0) {
+    if (lane == 0) {
+#pragma unroll
+      for (int b = 0; b < 5; b++) tc::mbar_init(&bars[b], 1);
+      tc::fence_mbar_init();
+    }
+    __syncwarp();
+    tc::tmem_alloc(tmem_slot, tmem_cols);
+    tc::tcgen05_fence_before();
+  }
+  __syncthreads();
+  tc::tcgen05_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  uint32_t step = 0;      // global MMA-step counter of this CTA (ring slot = step & 1)
+  uint32_t a_uses = 0;    // how many times the A planes have been handed to the tensor core
+  for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
+    const int64_t p0 = tile * kTile;
+    const int rows = (int)min((int64_t)kTile, a.n - p0);
+
+    // first B record of the tile: in flight during the statistics pass
+    if (tid == 0) {
+      const uint32_t slot = step & 1;
+      if (step >= 2 && !tc::mbar_wait(&bars[2 + slot], ((step >> 1) - 1) & 1))
+        atomicAdd(&g_ctc_timeouts, 1);
+      tc::mbar_arrive_expect_tx(&bars[slot], B::REC);
+      tc::tma_load_1d(s_b + slot * B::REC, a.mu_rec, B::REC, &bars[slot]);
+    }
+
+    // ---- pass 1: online softmax statistics of -E over all L labels ------------------------
+#pragma unroll 2
+    for (int i = 0; i < RPT; i++) {
+      const int r = g + i * 16;
+      float m = -INFINITY, s = 0.f;
+      if (r < rows) {
+        for (int c = l; c < a.L / 4; c += 16) {
+          const float4 e = *reinterpret_cast<const float4*>(e_ptr(a, p0 + r, 4 * c));
+          const float mx = fmaxf(fmaxf(-e.x, -e.y), fmaxf(-e.z, -e.w));
+          const float mn = fmaxf(m, mx);
+          s = s * __expf(m - mn) + __expf(-e.x - mn) + __expf(-e.y - mn) + __expf(-e.z - mn) +
+              __expf(-e.w - mn);
+          m = mn;
+        }
+      }
+      // combine the 16 lanes' (max, sum) pairs
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        const float m2 = __shfl_xor_sync(0xffffffffu, m, o, 16);
+        const float s2 = __shfl_xor_sync(0xffffffffu, s, o, 16);
+        const float mn = fmaxf(m, m2);
+        const float f1 = (m == -INFINITY) ? 0.f : __expf(m - mn);
+        const float f2 = (m2 == -INFINITY) ? 0.f : __expf(m2 - mn);
+        s = s * f1 + s2 * f2;
+        m = mn;
+      }
+      if (l == 0) {
+        s_m[r] = m;
+        s_inv[r] = (r < rows) ? __fdividef(1.0f, s) : 0.f;
+      }
+    }
+    __syncthreads();
+
+    // ---- pass 2: K chunks -------------------------------------------------------------------
+    for (int kc = 0; kc < KCH; kc++) {
+      // the tensor core must be done with the previous contents of the A planes
+      if (a_uses > 0 && !tc::mbar_wait(&bars[4], (a_uses - 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
+      tc::tcgen05_fence_after();
+#pragma unroll
+      for (int i = 0; i < RPT; i++) {
+        const int r = g + i * 16;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < rows) {
+          const float4 e = *reinterpret_cast<const float4*>(e_ptr(a, p0 + r, kc * kKC + 4 * l));
+          const float m = s_m[r], inv = s_inv[r];
+          x.x = __expf(-e.x - m) * inv;
+          x.y = __expf(-e.y - m) * inv;
+          x.z = __expf(-e.z - m) * inv;
+          x.w = __expf(-e.w - m) * inv;
+          if (a.q_out != nullptr)
+            *reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + kc * kKC + 4 * l) = x;
+        }
+        float4 hi, lo;
+        hi.x = tc::tf32_rna(x.x); lo.x = tc::tf32_rna(x.x - hi.x);
+        hi.y = tc::tf32_rna(x.y); lo.y = tc::tf32_rna(x.y - hi.y);
+        hi.z = tc::tf32_rna(x.z); lo.z = tc::tf32_rna(x.z - hi.z);
+        hi.w = tc::tf32_rna(x.w); lo.w = tc::tf32_rna(x.w - hi.w);
+        *reinterpret_cast<float4*>(s_a + l * kA_CH + r * 16) = hi;
+        *reinterpret_cast<float4*>(s_a + kA_BYTES + l * kA_CH + r * 16) = lo;
+      }
+      tc::fence_proxy_async();
+      __syncthreads();
+
+      if (tid == 0) {
+        tc::tcgen05_fence_after();
+        const uint32_t idesc = tc::idesc_tf32(kTile, BN);
+        const uint32_t a_hi = tc::smem_u32(s_a), a_lo = a_hi + kA_BYTES;
+        for (int nb = 0; nb < NB; nb++, step++) {
+          const uint32_t slot = step & 1;
+          // prefetch the next record of this tile into the other ring slot
+          const int nxt = kc * NB + nb + 1;
+          if (nxt < steps_per_tile) {
+            const uint32_t ns = (step + 1) & 1;
+            if (step + 1 >= 2 && !tc::mbar_wait(&bars[2 + ns], (((step + 1) >> 1) - 1) & 1))
+              atomicAdd(&g_ctc_timeouts, 1);
+            tc::mbar_arrive_expect_tx(&bars[ns], B::REC);
+            tc::tma_load_1d(s_b + ns * B::REC, a.mu_rec + (size_t)nxt * B::REC, B::REC, &bars[ns]);
+          }
+          if (!tc::mbar_wait(&bars[slot], (step >> 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
+          tc::tcgen05_fence_after();
+          const uint32_t b_hi = tc::smem_u32(s_b + slot * B::REC), b_lo = b_hi + B::B_BYTES;
+#pragma unroll
+          for (int pass = 0; pass < 3; pass++) {  // lo*hi, hi*lo, hi*hi
+            const uint32_t ab = (pass == 0) ? a_lo : a_hi;
+            const uint32_t bb = (pass == 1) ? b_lo : b_hi;
+#pragma unroll
+            for (int ks = 0; ks < kKC / 8; ks++) {
+              const uint64_t ad = tc::smem_desc_kmajor(ab + ks * 2 * kA_CH, kA_CH, 128);
+              const uint64_t bd = tc::smem_desc_kmajor(bb + ks * 2 * B::B_CH, B::B_CH, 128);
+              tc::mma_tf32_ss(tmem + (uint32_t)(nb * BN), ad, bd, idesc, (kc | pass | ks) != 0);
+            }
+          }
+          tc::mma_commit(&bars[2 + slot]);   // ring slot free once these MMAs have read it
+        }
+        tc::mma_commit(&bars[4]);            // A planes free (and, after the last chunk, P ready)
+      }
+      a_uses++;
+      __syncwarp();
+    }
+
+    // ---- epilogue: per 64-column block TMEM -> staging -> coalesced rows of P ---------------
+    if (!tc::mbar_wait(&bars[4], (a_uses - 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
+    __syncwarp();
+    tc::tcgen05_fence_after();
+    float* s_p = reinterpret_cast<float*>(s_a);
+    for (int c0 = 0; c0 < a.N; c0 += 64) {
+      const int cw = min(64, a.N - c0);          // 32 or 64
+      const int q = warp & 3, hsel = warp >> 2;  // TMEM lane quarter; column half of the block
+      const int row = q * 32 + lane;
+      const int cpw = cw / 2;                    // columns per warp: 16 or 32
+      for (int c8 = 0; c8 < cpw / 8; c8++) {
+        const int col = hsel * cpw + c8 * 8;
+        float v[8];
+        tc::tmem_ld_x8(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(c0 + col), v);
+        *reinterpret_cast<float4*>(s_p + row * kPLD + col) =
+            make_float4(v[0] * a.scale, v[1] * a.scale, v[2] * a.scale, v[3] * a.scale);
+        *reinterpret_cast<float4*>(s_p + row * kPLD + col + 4) =
+            make_float4(v[4] * a.scale, v[5] * a.scale, v[6] * a.scale, v[7] * a.scale);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < RPT; i++) {
+        const int r = g + i * 16;
+        if (r < rows && 4 * l < cw)
+          *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
+              *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
+      }
+      __syncthreads();
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();   // TMEM reads done before the next tile's first MMA overwrites it
+  }
+
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, tmem_cols);
+}
+
+// Mu[l0 + nb*BN + j][kc*64 + k] = muT[(kc*64 + k) * L + l0 + nb*BN + j]  ->  record (kc, nb):
+// hi plane | lo plane, each in the canonical K-major layout (16-byte K chunks of BN rows + pad).
+template <int BN>
+__global__ void __launch_bounds__(256)
+mu_records_kernel(const float* __restrict__ muT, int L, int l0, int N, uint8_t* __restrict__ out) {
+  using B = BCfg<BN>;
+  const int NB = N / BN;
+  const int nrec = (L / kKC) * NB;
+  const int plane_floats = B::B_BYTES / 4;
+  const int chunk_floats = B::B_CH / 4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nrec * plane_floats;
+       i += gridDim.x * blockDim.x) {
+    const int rec = i / plane_floats, w = i - rec * plane_floats;
+    const int kc = rec / NB, nb = rec - kc * NB;
+    const int ch = w / chunk_floats, rem = w - ch * chunk_floats;
+    float hi = 0.f, lo = 0.f;
+    if (rem < BN * 4) {
+      const int j = rem >> 2, k = kc * kKC + ch * 4 + (rem & 3);
+      const float m = muT[(int64_t)k * L + l0 + nb * BN + j];
+      hi = tc::tf32_rna(m);
+      lo = tc::tf32_rna(m - hi);
+    }
+    float* base = reinterpret_cast<float*>(out + (size_t)rec * B::REC);
+    base[w] = hi;
+    base[plane_floats + w] = lo;
+  }
+}
+
+template <int BN>
+size_t ctc_smem() {
+  return 2 * (size_t)kA_BYTES + 2 * (size_t)BCfg<BN>::REC + 2 * kTile * 4 + 5 * 8 + 16;
+}
+
+template <int BN>
+int launch_ctc(const CArgs& a, cudaStream_t st) {
+  const size_t smem = ctc_smem<BN>();
+  static bool done = false;
+  if (!done) {
+    PL_CUDA(cudaFuncSetAttribute(compat_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem));
+    done = true;
+  }
+  const unsigned grid = (unsigned)(a.ntiles < PL_SM_COUNT ? a.ntiles : PL_SM_COUNT);
+  PL_LAUNCH((compat_tc_kernel<BN>), grid, kThreads, smem, st, a);
+  return PL_OK;
+}
+
+}  // namespace
+
+// Output labels l0 .. l0+N of a model with L labels.  Supported: L % 64 == 0, N % 32 == 0,
+// 32 <= N <= 256, and the blocked input layout must not split a float4 (block_w % 4 == 0).
+bool compat_tc_supported(int L, int N, int block_w) {
+  return L >= 64 && L % 64 == 0 && N >= 32 && N <= 256 && N % 32 == 0 && block_w % 4 == 0 &&
+         L % block_w == 0;
+}
+
+size_t compat_tc_mu_bytes(int L, int N) {
+  const int BN = (N % 64 == 0) ? 64 : 32;
+  const size_t rec = BN == 64 ? BCfg<64>::REC : BCfg<32>::REC;
+  return (size_t)(L / kKC) * (N / BN) * rec;
+}
+
+int compat_tc_prepare_mu(const float* muT, int L, int l0, int N, uint8_t* mu_rec, cudaStream_t st) {
+  if (N % 64 == 0) {
+    PL_LAUNCH((mu_records_kernel<64>), 64, 256, 0, st, muT, L, l0, N, mu_rec);
+  } else {
+    PL_LAUNCH((mu_records_kernel<32>), 64, 256, 0, st, muT, L, l0, N, mu_rec);
+  }
+  return PL_OK;
+}
+
+int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_rec, float* p,
+                  float* q_out, int64_t n, int L, int N, float scale, cudaStream_t st) {
+  CArgs a;
+  a.e = e; a.nblocks = nblocks; a.block_w = block_w; a.mu_rec = mu_rec; a.p = p; a.q_out = q_out;
+  a.n = n; a.ntiles = (n + kTile - 1) / kTile; a.L = L; a.N = N; a.scale = scale;
+  if (N % 64 == 0) return launch_ctc<64>(a, st);
+  return launch_ctc<32>(a, st);
+}
+
+int ctc_timeouts() {
+  int v = 0;
+  cudaMemcpyFromSymbol(&v, g_ctc_timeouts, sizeof(int));
+  return v;
+}
+
+}  // namespace pl

@@ -125,6 +125,18 @@ int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, fl
 int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
                          int64_t n, int L, float scale, uint32_t flags, void* stream);
 
+/* Label-sharded form of the same transform (label-channel sharding, one all-gather
+ * per mean-field iteration).  The caller holds E for ALL L labels in the blocked layout an
+ * all-gather over G label shards produces, e_blocks_dev[b][p][w] with b < nblocks,
+ * w < L / nblocks, label = b * (L / nblocks) + w (nblocks = 1: plain [n][L]); the softmax runs
+ * over all L labels and the rank computes its own N output labels l0 .. l0+N-1:
+ *   p_dev[p][j] = scale * sum_k Mu[l0 + j][k] * softmax_k(-E[p][.])[k],  p_dev is [n][N].
+ * muT_dev is the full transposed matrix [L(k)][L(l)].  tcgen05 path (3xTF32) when
+ * L % 64 == 0 and N % 32 == 0, N <= 256; otherwise PL_ERR_INVALID. */
+int pl_softmax_compat_blocked(const float* e_blocks_dev, int nblocks, const float* muT_dev,
+                              float* p_dev, int64_t n, int L, int l0, int N, float scale,
+                              void* stream);
+
 /* Whole inference loop of CRFasRNN.forward (crf_module.py:93-104) with
  * W = lattice adjacency (gaussian_matrix.py:341-352), pixel-major:
  *   E = E0; repeat niters: P = scale * Mu softmax(-E); E = E0 + filter(P) - P

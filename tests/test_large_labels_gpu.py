@@ -1,0 +1,90 @@
+"""Large label counts (L = 128, 256) and label sharding on the GPU.
+
+* pl_softmax_compat_blocked (pl_compat_tc.cu): tcgen05 3xTF32 contraction with K = L, N = shard
+  width, blocked (all-gathered) E layout -- against fp64.
+* the label-sharded mean-field loop, G ranks emulated one after another in one process on one
+  GPU (ranks must not spin on each other on a single device), against the unsharded loop and
+  the CPU oracle.
+"""
+import ctypes as C
+import importlib
+
+import numpy as np
+import pytest
+import torch
+
+synthetic = importlib.import_module("depth_estimation_b200.synthetic")
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("L,G", [(128, 1), (128, 2), (256, 1), (256, 4), (256, 8), (64, 2), (192, 3)])
+def test_blocked_compat_tensor_core(native, L, G):
+    N = native._native
+    w = L // G
+    for n in (1, 130, 777):
+        g = torch.Generator().manual_seed(L * 7 + G + n)
+        e = torch.randn((n, L), generator=g) * 3
+        mu = torch.from_numpy(synthetic.charb_matrix(L)) + torch.rand((L, L), generator=g) * 0.1
+        q = torch.softmax(-e.double(), dim=1)
+        want = (q @ mu.double().t()) * 0.9
+        blocks = e.reshape(n, G, w).permute(1, 0, 2).contiguous().cuda()     # [G][n][w]
+        mt = mu.t().contiguous().cuda()
+        for rank in range(G):
+            p = torch.full((n, w), float("nan"), device="cuda")
+            N.check(N.lib().pl_softmax_compat_blocked(
+                C.c_void_p(blocks.data_ptr()), G, C.c_void_p(mt.data_ptr()), C.c_void_p(p.data_ptr()),
+                n, L, rank * w, w, 0.9, N.stream_ptr(p.device)))
+            torch.cuda.synchronize()
+            assert _rel(p, want[:, rank * w:(rank + 1) * w]) < 1e-5, (L, G, n, rank)   # fast exp + online softmax rescaling
+    assert N.lib().pl_debug_tc_timeouts() == 0
+
+
+class _FakeGroupRun:
+    """Runs LabelShardedMeanField's iteration for all ranks in lock step on one device."""
+
+    def __init__(self, native, lat, world):
+        ls = importlib.import_module("depth_estimation_b200.crf.label_shards")
+        self.ls, self.world = ls, world
+        self.backend = ls.CudaBackend(lat)
+
+    def run(self, e0, mu, niters, scale):
+        n, L = e0.shape
+        w = L // self.world
+        mu_t = mu.t().contiguous()
+        shards0 = [e0[:, r * w:(r + 1) * w].contiguous() for r in range(self.world)]
+        shards = list(shards0)
+        for _ in range(niters):
+            blocks = torch.stack(shards)                       # what the all-gather delivers
+            shards = [self.backend.filter_update(
+                self.backend.compat(blocks, mu_t, r * w, w, scale), shards0[r])
+                for r in range(self.world)]
+        return torch.cat(shards, dim=1)
+
+
+@pytest.mark.parametrize("h,w,L,G,niters", [(24, 32, 128, 4, 3), (20, 28, 256, 8, 2), (20, 28, 256, 2, 2)])
+def test_label_sharded_mean_field_matches_unsharded_and_oracle(native, oracle, h, w, L, G, niters):
+    ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=L))
+    e0 = synthetic.unary(h, w, L, seed=L)
+    mu = synthetic.charb_matrix(L) * 0.3
+    hdl = oracle.build(ref)
+    e = e0.copy()
+    for _ in range(niters):
+        x = -e - (-e).max(1, keepdims=True)
+        q = np.exp(x) / np.exp(x).sum(1, keepdims=True)
+        p = (q @ mu.T).astype(np.float32) * np.float32(1.1)
+        e = e0 + (hdl.apply(p) - p)
+    lat = native.PermutohedralLattice(torch.from_numpy(ref).cuda())
+    e0d, mud = torch.from_numpy(e0).cuda(), torch.from_numpy(mu).cuda()
+    unsharded = lat.mean_field(e0d, mud, niters, 1.1).cpu().numpy()          # large-L path
+    cuda_core = lat.mean_field(e0d, mud, niters, 1.1, no_tensor=True).cpu().numpy()
+    sharded = _FakeGroupRun(native, lat, G).run(e0d, mud, niters, 1.1).cpu().numpy()
+    scale = np.abs(e).max()
+    for got in (unsharded, cuda_core, sharded):
+        assert np.abs(got - e).max() / scale < 2e-4
+        assert (got.argmin(1) == e.argmin(1)).mean() > 0.999
+    assert native._native.lib().pl_debug_tc_timeouts() == 0
