@@ -18,6 +18,7 @@
 // E may be given in the BLOCKED layout an all-gather over label shards produces:
 // e[b][p][lw] with b < nblocks, lw < block_w, label = b * block_w + lw  (nblocks = 1: plain [n][L]).
 #include <math.h>
+#include <stdlib.h>
 
 #include "pl_common.cuh"
 #include "pl_tc.cuh"
@@ -27,11 +28,13 @@ namespace pl {
 namespace {
 
 constexpr int kTile = PL_TILE;  // 128
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;
 constexpr int kKC = 64;                          // K chunk (labels per A / B record)
 constexpr int kA_CH = kTile * 16 + 16;           // bytes per 16-byte K chunk column of A
 constexpr int kA_BYTES = (kKC / 4) * kA_CH;      // one plane of A: 33024
 constexpr int kPLD = 64 + 4;                     // epilogue staging pitch (floats)
+constexpr int kRing = 2;                         // Mu records in flight (TMA ring slots)
+constexpr int kSup = 1;                          // 128-pixel tiles per Mu record pass (2 halves the L2 traffic of Mu but measured slower: the kernel is latency-bound, not L2-bound)
 
 __device__ int g_ctc_timeouts = 0;
 
@@ -51,37 +54,37 @@ struct CArgs {
   int64_t n, ntiles;
   int L, N;
   float scale;
+  int debug;  // timing experiments only: 1 = no MMAs, 2 = no statistics pass, 4 = no epilogue
 };
 
-__device__ __forceinline__ const float* e_ptr(const CArgs& a, int64_t p, int label) {
-  const int b = label / a.block_w;
-  return a.e + ((int64_t)b * a.n + p) * a.block_w + (label - b * a.block_w);
-}
+constexpr int kMaxKC = 8;  // L <= 512
 
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
   using B = BCfg<BN>;
   extern __shared__ __align__(128) unsigned char smem[];
   unsigned char* s_a = smem;                       // A hi | lo planes; epilogue staging
-  unsigned char* s_b = smem + 2 * kA_BYTES;        // two B records (ring)
-  float* s_m = reinterpret_cast<float*>(s_b + 2 * B::REC);   // [128] row max of -E
-  float* s_inv = s_m + kTile;                                // [128] 1 / row sum
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + kTile);
-  // bars: [0,1] B record landed (ring slot)  [2,3] ring slot free  [4] all MMAs on A done
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+  unsigned char* s_b = smem + kSup * 2 * kA_BYTES;  // kRing B records (ring)
+  float* s_m = reinterpret_cast<float*>(s_b + kRing * B::REC);   // [128] row max of -E
+  float* s_inv = s_m + kSup * kTile;                         // 1 / row sum
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_inv + kSup * kTile);
+  // bars: [0..R) B record landed (ring slot)  [R..2R) ring slot free  [2R] all MMAs on A done
+  constexpr int kBarA = 2 * kRing;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kBarA + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int g = tid >> 4, l = tid & 15;   // 16 lanes per pixel row, 16 rows per pass
-  constexpr int RPT = kTile / 16;         // 8 rows per thread
+  const int g = tid >> 4, l = tid & 15;   // 16 lanes per pixel row
+  constexpr int RPP = kThreads / 16;      // rows per pass (32)
+  constexpr int RPT = kSup * kTile / RPP; // rows per thread (8), over the kSup tiles
   const int KCH = a.L / kKC;              // K chunks
   const int NB = a.N / BN;                // output blocks
   const int steps_per_tile = KCH * NB;
-  const uint32_t tmem_cols = a.N <= 32 ? 32 : (a.N <= 64 ? 64 : (a.N <= 128 ? 128 : 256));
+  const uint32_t tmem_cols = kSup * (a.N <= 32 ? 32 : (a.N <= 64 ? 64 : (a.N <= 128 ? 128 : 256)));
 
   if (warp == 0) {
     if (lane == 0) {
 #pragma unroll
-      for (int b = 0; b < 5; b++) tc::mbar_init(&bars[b], 1);
+      for (int b = 0; b <= kBarA; b++) tc::mbar_init(&bars[b], 1);
       tc::fence_mbar_init();
     }
     __syncwarp();
@@ -92,70 +95,112 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
   tc::tcgen05_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  uint32_t step = 0;      // global MMA-step counter of this CTA (ring slot = step & 1)
-  uint32_t a_uses = 0;    // how many times the A planes have been handed to the tensor core
-  for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
-    const int64_t p0 = tile * kTile;
-    const int rows = (int)min((int64_t)kTile, a.n - p0);
+  // Where this thread's float4 of K chunk kc lives, without the pixel term: the blocked
+  // layout puts label (b * block_w + w) of pixel p at e[(b * n + p) * block_w + w].
+  int64_t eoff[kMaxKC];
+#pragma unroll
+  for (int kc = 0; kc < kMaxKC; kc++) {
+    const int label = kc * kKC + 4 * l;
+    const int b = label / a.block_w;
+    eoff[kc] = (int64_t)b * a.n * a.block_w + (label - b * a.block_w);
+  }
+  const int64_t bw = a.block_w;
 
-    // first B record of the tile: in flight during the statistics pass
-    if (tid == 0) {
-      const uint32_t slot = step & 1;
-      if (step >= 2 && !tc::mbar_wait(&bars[2 + slot], ((step >> 1) - 1) & 1))
-        atomicAdd(&g_ctc_timeouts, 1);
-      tc::mbar_arrive_expect_tx(&bars[slot], B::REC);
-      tc::tma_load_1d(s_b + slot * B::REC, a.mu_rec, B::REC, &bars[slot]);
-    }
+  // Every tile consumes the same sequence of Mu records, so the ring simply cycles: global step
+  // t of this CTA uses record t % steps_per_tile in slot t % kRing; requests run kRing-1 ahead.
+  const uint32_t my_tiles = (uint32_t)((a.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
+  const uint32_t total_steps = my_tiles * (uint32_t)steps_per_tile;
+  auto request = [&](uint32_t t) {   // tid 0 only
+    const uint32_t slot = t % kRing, use = t / kRing;
+    if (use > 0 && !tc::mbar_wait(&bars[kRing + slot], (use - 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
+    tc::mbar_arrive_expect_tx(&bars[slot], B::REC);
+    tc::tma_load_1d(s_b + slot * B::REC, a.mu_rec + (size_t)(t % steps_per_tile) * B::REC, B::REC,
+                    &bars[slot]);
+  };
+  if (tid == 0)
+    for (uint32_t t = 0; t < kRing - 1 && t < total_steps; t++) request(t);
+
+  uint32_t step = 0;      // global MMA-step counter of this CTA
+  uint32_t a_uses = 0;    // how many times the A planes have been handed to the tensor core
+  const uint32_t ncols1 = tmem_cols / kSup;   // TMEM columns per 128-pixel tile
+  for (int64_t st = blockIdx.x; st < a.ntiles; st += gridDim.x) {   // super-tiles of kSup tiles
+    const int64_t p0 = st * (kSup * kTile);
+    const int rows = (int)min((int64_t)(kSup * kTile), a.n - p0);
 
     // ---- pass 1: online softmax statistics of -E over all L labels ------------------------
-#pragma unroll 2
-    for (int i = 0; i < RPT; i++) {
-      const int r = g + i * 16;
-      float m = -INFINITY, s = 0.f;
-      if (r < rows) {
-        for (int c = l; c < a.L / 4; c += 16) {
-          const float4 e = *reinterpret_cast<const float4*>(e_ptr(a, p0 + r, 4 * c));
-          const float mx = fmaxf(fmaxf(-e.x, -e.y), fmaxf(-e.z, -e.w));
-          const float mn = fmaxf(m, mx);
-          s = s * __expf(m - mn) + __expf(-e.x - mn) + __expf(-e.y - mn) + __expf(-e.z - mn) +
-              __expf(-e.w - mn);
-          m = mn;
+    // RPT independent rows per thread advance together: RPT loads in flight per step
+    {
+      float m[RPT], sum[RPT];
+#pragma unroll
+      for (int i = 0; i < RPT; i++) {
+        m[i] = -INFINITY;
+        sum[i] = 0.f;
+      }
+#pragma unroll
+      for (int kc = 0; kc < kMaxKC; kc++) {
+        if (kc >= KCH || (a.debug & 2)) break;
+        float4 e[RPT];
+#pragma unroll
+        for (int i = 0; i < RPT; i++) {
+          const int r = g + i * RPP;
+          e[i] = (r < rows) ? *reinterpret_cast<const float4*>(a.e + eoff[kc] + (p0 + r) * bw)
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < RPT; i++) {
+          const float mx = fmaxf(fmaxf(-e[i].x, -e[i].y), fmaxf(-e[i].z, -e[i].w));
+          const float mn = fmaxf(m[i], mx);
+          sum[i] = sum[i] * __expf(m[i] - mn) + __expf(-e[i].x - mn) + __expf(-e[i].y - mn) +
+                   __expf(-e[i].z - mn) + __expf(-e[i].w - mn);
+          m[i] = mn;
         }
       }
-      // combine the 16 lanes' (max, sum) pairs
 #pragma unroll
-      for (int o = 8; o > 0; o >>= 1) {
-        const float m2 = __shfl_xor_sync(0xffffffffu, m, o, 16);
-        const float s2 = __shfl_xor_sync(0xffffffffu, s, o, 16);
-        const float mn = fmaxf(m, m2);
-        const float f1 = (m == -INFINITY) ? 0.f : __expf(m - mn);
-        const float f2 = (m2 == -INFINITY) ? 0.f : __expf(m2 - mn);
-        s = s * f1 + s2 * f2;
-        m = mn;
-      }
-      if (l == 0) {
-        s_m[r] = m;
-        s_inv[r] = (r < rows) ? __fdividef(1.0f, s) : 0.f;
+      for (int i = 0; i < RPT; i++) {
+        const int r = g + i * RPP;
+        float mi = m[i], si = sum[i];
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {  // combine the 16 lanes' (max, sum) pairs
+          const float m2 = __shfl_xor_sync(0xffffffffu, mi, o, 16);
+          const float s2 = __shfl_xor_sync(0xffffffffu, si, o, 16);
+          const float mn = fmaxf(mi, m2);
+          si = si * __expf(mi - mn) + s2 * __expf(m2 - mn);
+          mi = mn;
+        }
+        if (l == 0) {
+          s_m[r] = mi;
+          s_inv[r] = (r < rows) ? __fdividef(1.0f, si) : 0.f;
+        }
       }
     }
     __syncthreads();
 
     // ---- pass 2: K chunks -------------------------------------------------------------------
-    for (int kc = 0; kc < KCH; kc++) {
+#pragma unroll
+    for (int kc = 0; kc < kMaxKC; kc++) {
+      if (kc >= KCH) break;
+      // this chunk's E values first: the loads overlap the MMAs still reading the previous
+      // chunk's A planes
+      float4 e[RPT];
+#pragma unroll
+      for (int i = 0; i < RPT; i++) {
+        const int r = g + i * RPP;
+        e[i] = (r < rows) ? *reinterpret_cast<const float4*>(a.e + eoff[kc] + (p0 + r) * bw)
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       // the tensor core must be done with the previous contents of the A planes
-      if (a_uses > 0 && !tc::mbar_wait(&bars[4], (a_uses - 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
+      if (a_uses > 0 && !tc::mbar_wait(&bars[kBarA], (a_uses - 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
       tc::tcgen05_fence_after();
 #pragma unroll
       for (int i = 0; i < RPT; i++) {
-        const int r = g + i * 16;
+        const int r = g + i * RPP;
         float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
         if (r < rows) {
-          const float4 e = *reinterpret_cast<const float4*>(e_ptr(a, p0 + r, kc * kKC + 4 * l));
           const float m = s_m[r], inv = s_inv[r];
-          x.x = __expf(-e.x - m) * inv;
-          x.y = __expf(-e.y - m) * inv;
-          x.z = __expf(-e.z - m) * inv;
-          x.w = __expf(-e.w - m) * inv;
+          x.x = __expf(-e[i].x - m) * inv;
+          x.y = __expf(-e[i].y - m) * inv;
+          x.z = __expf(-e[i].z - m) * inv;
+          x.w = __expf(-e[i].w - m) * inv;
           if (a.q_out != nullptr)
             *reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + kc * kKC + 4 * l) = x;
         }
@@ -164,8 +209,10 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         hi.y = tc::tf32_rna(x.y); lo.y = tc::tf32_rna(x.y - hi.y);
         hi.z = tc::tf32_rna(x.z); lo.z = tc::tf32_rna(x.z - hi.z);
         hi.w = tc::tf32_rna(x.w); lo.w = tc::tf32_rna(x.w - hi.w);
-        *reinterpret_cast<float4*>(s_a + l * kA_CH + r * 16) = hi;
-        *reinterpret_cast<float4*>(s_a + kA_BYTES + l * kA_CH + r * 16) = lo;
+        // tile t = r / 128 of the super-tile has its own pair of planes
+        unsigned char* pa = s_a + (r >> 7) * (2 * kA_BYTES) + l * kA_CH + (r & 127) * 16;
+        *reinterpret_cast<float4*>(pa) = hi;
+        *reinterpret_cast<float4*>(pa + kA_BYTES) = lo;
       }
       tc::fence_proxy_async();
       __syncthreads();
@@ -173,71 +220,73 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
       if (tid == 0) {
         tc::tcgen05_fence_after();
         const uint32_t idesc = tc::idesc_tf32(kTile, BN);
-        const uint32_t a_hi = tc::smem_u32(s_a), a_lo = a_hi + kA_BYTES;
         for (int nb = 0; nb < NB; nb++, step++) {
-          const uint32_t slot = step & 1;
-          // prefetch the next record of this tile into the other ring slot
-          const int nxt = kc * NB + nb + 1;
-          if (nxt < steps_per_tile) {
-            const uint32_t ns = (step + 1) & 1;
-            if (step + 1 >= 2 && !tc::mbar_wait(&bars[2 + ns], (((step + 1) >> 1) - 1) & 1))
-              atomicAdd(&g_ctc_timeouts, 1);
-            tc::mbar_arrive_expect_tx(&bars[ns], B::REC);
-            tc::tma_load_1d(s_b + ns * B::REC, a.mu_rec + (size_t)nxt * B::REC, B::REC, &bars[ns]);
-          }
-          if (!tc::mbar_wait(&bars[slot], (step >> 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
+          const uint32_t slot = step % kRing;
+          if (!tc::mbar_wait(&bars[slot], (step / kRing) & 1)) atomicAdd(&g_ctc_timeouts, 1);
           tc::tcgen05_fence_after();
           const uint32_t b_hi = tc::smem_u32(s_b + slot * B::REC), b_lo = b_hi + B::B_BYTES;
 #pragma unroll
-          for (int pass = 0; pass < 3; pass++) {  // lo*hi, hi*lo, hi*hi
-            const uint32_t ab = (pass == 0) ? a_lo : a_hi;
-            const uint32_t bb = (pass == 1) ? b_lo : b_hi;
+          for (int t = 0; t < kSup; t++) {   // one Mu record feeds both tiles of the super-tile
+            const uint32_t a_hi = tc::smem_u32(s_a) + t * (2 * kA_BYTES), a_lo = a_hi + kA_BYTES;
 #pragma unroll
-            for (int ks = 0; ks < kKC / 8; ks++) {
-              const uint64_t ad = tc::smem_desc_kmajor(ab + ks * 2 * kA_CH, kA_CH, 128);
-              const uint64_t bd = tc::smem_desc_kmajor(bb + ks * 2 * B::B_CH, B::B_CH, 128);
-              tc::mma_tf32_ss(tmem + (uint32_t)(nb * BN), ad, bd, idesc, (kc | pass | ks) != 0);
+            for (int pass = 0; pass < 3; pass++) {  // lo*hi, hi*lo, hi*hi
+              const uint32_t ab = (pass == 0) ? a_lo : a_hi;
+              const uint32_t bb = (pass == 1) ? b_lo : b_hi;
+#pragma unroll
+              for (int ks = 0; ks < kKC / 8; ks++) {
+                const uint64_t ad = tc::smem_desc_kmajor(ab + ks * 2 * kA_CH, kA_CH, 128);
+                const uint64_t bd = tc::smem_desc_kmajor(bb + ks * 2 * B::B_CH, B::B_CH, 128);
+                if (!(a.debug & 1))
+                  tc::mma_tf32_ss(tmem + t * ncols1 + (uint32_t)(nb * BN), ad, bd, idesc,
+                                  (kc | pass | ks) != 0);
+              }
             }
           }
-          tc::mma_commit(&bars[2 + slot]);   // ring slot free once these MMAs have read it
+          tc::mma_commit(&bars[kRing + slot]);   // ring slot free once these MMAs have read it
+          if (step + kRing - 1 < total_steps) request(step + kRing - 1);
         }
-        tc::mma_commit(&bars[4]);            // A planes free (and, after the last chunk, P ready)
+        tc::mma_commit(&bars[kBarA]);            // A planes free (and, after the last chunk, P ready)
       }
       a_uses++;
       __syncwarp();
     }
 
-    // ---- epilogue: per 64-column block TMEM -> staging -> coalesced rows of P ---------------
-    if (!tc::mbar_wait(&bars[4], (a_uses - 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
+    // ---- epilogue: per tile, per 64-column block TMEM -> staging -> coalesced rows of P ------
+    if (!tc::mbar_wait(&bars[kBarA], (a_uses - 1) & 1)) atomicAdd(&g_ctc_timeouts, 1);
     __syncwarp();
     tc::tcgen05_fence_after();
     float* s_p = reinterpret_cast<float*>(s_a);
-    for (int c0 = 0; c0 < a.N; c0 += 64) {
-      const int cw = min(64, a.N - c0);          // 32 or 64
-      const int q = warp & 3, hsel = warp >> 2;  // TMEM lane quarter; column half of the block
-      const int row = q * 32 + lane;
-      const int cpw = cw / 2;                    // columns per warp: 16 or 32
-      for (int c8 = 0; c8 < cpw / 8; c8++) {
-        const int col = hsel * cpw + c8 * 8;
-        float v[8];
-        tc::tmem_ld_x8(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(c0 + col), v);
-        *reinterpret_cast<float4*>(s_p + row * kPLD + col) =
-            make_float4(v[0] * a.scale, v[1] * a.scale, v[2] * a.scale, v[3] * a.scale);
-        *reinterpret_cast<float4*>(s_p + row * kPLD + col + 4) =
-            make_float4(v[4] * a.scale, v[5] * a.scale, v[6] * a.scale, v[7] * a.scale);
-      }
-      __syncthreads();
+    for (int t = 0; t < kSup; t++) {
+      if (t * kTile >= rows) break;
+      for (int c0 = 0; c0 < ((a.debug & 4) ? 0 : a.N); c0 += 64) {
+        const int cw = min(64, a.N - c0);          // 32 or 64
+        const int q = warp & 3, hsel = warp >> 2;  // TMEM lane quarter; column group of the block
+        const int row = q * 32 + lane;
+        constexpr int NCG = kThreads / 128;        // column groups (4)
+        const int cpw = cw / NCG;                  // columns per warp: 8 or 16
+        for (int c8 = 0; c8 < cpw / 8; c8++) {
+          const int col = hsel * cpw + c8 * 8;
+          float v[8];
+          tc::tmem_ld_x8(tmem + ((uint32_t)(q * 32) << 16) + t * ncols1 + (uint32_t)(c0 + col), v);
+          *reinterpret_cast<float4*>(s_p + row * kPLD + col) =
+              make_float4(v[0] * a.scale, v[1] * a.scale, v[2] * a.scale, v[3] * a.scale);
+          *reinterpret_cast<float4*>(s_p + row * kPLD + col + 4) =
+              make_float4(v[4] * a.scale, v[5] * a.scale, v[6] * a.scale, v[7] * a.scale);
+        }
+        __syncthreads();
+        // 128 rows x cw columns, 16 lanes per row, 32 rows per pass
 #pragma unroll
-      for (int i = 0; i < RPT; i++) {
-        const int r = g + i * 16;
-        if (r < rows && 4 * l < cw)
-          *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
-              *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
+        for (int i = 0; i < kTile / RPP; i++) {
+          const int r = g + i * RPP;
+          if (t * kTile + r < rows && 4 * l < cw)
+            *reinterpret_cast<float4*>(a.p + (p0 + t * kTile + r) * a.N + c0 + 4 * l) =
+                *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
+        }
+        __syncthreads();
       }
-      __syncthreads();
     }
     tc::tcgen05_fence_before();
-    __syncthreads();   // TMEM reads done before the next tile's first MMA overwrites it
+    __syncthreads();   // TMEM reads done before the next super-tile's first MMA overwrites it
   }
 
   __syncthreads();
@@ -274,7 +323,8 @@ mu_records_kernel(const float* __restrict__ muT, int L, int l0, int N, uint8_t* 
 
 template <int BN>
 size_t ctc_smem() {
-  return 2 * (size_t)kA_BYTES + 2 * (size_t)BCfg<BN>::REC + 2 * kTile * 4 + 5 * 8 + 16;
+  return kSup * 2 * (size_t)kA_BYTES + kRing * (size_t)BCfg<BN>::REC + kSup * 2 * kTile * 4 +
+         (2 * kRing + 1) * 8 + 16;
 }
 
 template <int BN>
@@ -296,7 +346,7 @@ int launch_ctc(const CArgs& a, cudaStream_t st) {
 // Output labels l0 .. l0+N of a model with L labels.  Supported: L % 64 == 0, N % 32 == 0,
 // 32 <= N <= 256, and the blocked input layout must not split a float4 (block_w % 4 == 0).
 bool compat_tc_supported(int L, int N, int block_w) {
-  return L >= 64 && L % 64 == 0 && N >= 32 && N <= 256 && N % 32 == 0 && block_w % 4 == 0 &&
+  return L >= 64 && L <= kMaxKC * kKC && L % 64 == 0 && N >= 32 && N <= 256 && N % 32 == 0 && block_w % 4 == 0 &&
          L % block_w == 0;
 }
 
@@ -319,7 +369,8 @@ int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_re
                   float* q_out, int64_t n, int L, int N, float scale, cudaStream_t st) {
   CArgs a;
   a.e = e; a.nblocks = nblocks; a.block_w = block_w; a.mu_rec = mu_rec; a.p = p; a.q_out = q_out;
-  a.n = n; a.ntiles = (n + kTile - 1) / kTile; a.L = L; a.N = N; a.scale = scale;
+  a.n = n; a.ntiles = (n + kSup * kTile - 1) / (kSup * kTile); a.L = L; a.N = N; a.scale = scale;
+  a.debug = getenv("PL_CTC_DEBUG") ? atoi(getenv("PL_CTC_DEBUG")) : 0;
   if (N % 64 == 0) return launch_ctc<64>(a, st);
   return launch_ctc<32>(a, st);
 }
