@@ -446,6 +446,12 @@ def main():
     ap.add_argument("--only-step", action="store_true",
                     help="run warm-up + timed device-resident steps only (for ncu)")
     args = ap.parse_args()
+    # The JSON line must be the only thing on stdout: libraries that printf to fd 1 (NCCL's
+    # version banner under NCCL_DEBUG) go to stderr, python's print keeps the real stdout.
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

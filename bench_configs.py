@@ -200,6 +200,10 @@ def main():
     ap.add_argument("--profile", action="store_true", help="per-kernel CUDA-event times of one step")
     ap.add_argument("--frames", type=int, default=0)
     args = ap.parse_args()
+    sys.stdout.flush()          # only JSON lines on stdout (NCCL's banner goes to stderr)
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
     import torch
     import torch.distributed as dist
     rank = int(os.environ.get("RANK", "0"))
