@@ -20,6 +20,7 @@ PL_APPLY_EXACT_SLICE = 1
 PL_APPLY_FLAT_KERNELS = 2
 PL_MEANFIELD_UNFUSED = 4
 PL_MEANFIELD_NO_TENSOR = 8
+PL_MEANFIELD_TILE_KERNEL = 16
 (PL_EXPORT_GREEDY, PL_EXPORT_RANK, PL_EXPORT_BARY, PL_EXPORT_VERTEX, PL_EXPORT_KEYS,
  PL_EXPORT_NEIGHBOURS) = range(6)
 

@@ -78,7 +78,7 @@ class PermutohedralLattice:
     __call__ = filter
 
     def mean_field(self, e0, mu, niters, scale=1.0, exact_slice=False, flat=False, unfused=False,
-                   no_tensor=False):
+                   no_tensor=False, tile_kernel=False):
         """Pixel-major CRFasRNN inference loop (crf_module.py:97-103).
 
         ``e0[n, L]`` unary energies, ``mu[L, L]`` compatibility matrix
@@ -95,7 +95,8 @@ class PermutohedralLattice:
         work = torch.empty_like(e0)
         flags = ((N.PL_APPLY_EXACT_SLICE if exact_slice else 0) | (N.PL_APPLY_FLAT_KERNELS if flat else 0)
                  | (N.PL_MEANFIELD_UNFUSED if unfused else 0)
-                 | (N.PL_MEANFIELD_NO_TENSOR if no_tensor else 0))
+                 | (N.PL_MEANFIELD_NO_TENSOR if no_tensor else 0)
+                 | (N.PL_MEANFIELD_TILE_KERNEL if tile_kernel else 0))
         with torch.cuda.device(self.device):
             N.check(N.lib().pl_meanfield(
                 self._h, C.c_void_p(e0.data_ptr()), C.c_void_p(mu_t.data_ptr()),

@@ -86,6 +86,9 @@ int64_t pl_lattice_device_bytes(const pl_lattice* lat); /* persistent device mem
 /* pl_meanfield / pl_softmax_compat: keep the compatibility transform on the CUDA cores
  * (fp32 FMA, k ascending) instead of the tcgen05 3xTF32 path used for L in {16, 32, 64}. */
 #define PL_MEANFIELD_NO_TENSOR 8u
+/* pl_meanfield: use the tile form of the tcgen05 iteration kernel (pl_fused_tc.cu, two CTAs per
+ * SM) even where the row-per-thread form (pl_fused_row.cu; L in {32, 64}, d = 5) exists. */
+#define PL_MEANFIELD_TILE_KERNEL 16u
 
 /* dst[p][c] = filter(src)[p][c] - (sub ? sub[p][c] : 0) + (add ? add[p][c] : 0)
  *

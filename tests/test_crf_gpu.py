@@ -211,7 +211,9 @@ def test_stereo_wrappers_run(native):
 
 
 @pytest.mark.parametrize("h,w,L,niters,s_ij", [(37, 53, 4, 1, 0.1), (48, 64, 16, 5, 0.1), (50, 70, 40, 2, 0.1),
-                                                 (64, 96, 64, 3, 0.1), (40, 60, 64, 4, 0.01)])
+                                                 (64, 96, 64, 3, 0.1), (40, 60, 64, 4, 0.01),
+                                                 (150, 201, 64, 3, 0.1), (240, 321, 32, 3, 0.1),
+                                                 (90, 130, 32, 2, 0.02)])
 def test_fused_iteration_matches_unfused_and_oracle(native, oracle, h, w, L, niters, s_ij):
     """pl_meanfield: fused per-iteration kernel (pl_fused.cu) vs separate kernels vs CPU oracle."""
     ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=L), s_ij, 0.1)
@@ -231,8 +233,9 @@ def test_fused_iteration_matches_unfused_and_oracle(native, oracle, h, w, L, nit
     unfused = lat.mean_field(e0d, mud, niters, 1.3, unfused=True).cpu().numpy()
     flat = lat.mean_field(e0d, mud, niters, 1.3, flat=True).cpu().numpy()
     cuda_core = lat.mean_field(e0d, mud, niters, 1.3, no_tensor=True).cpu().numpy()
+    tile = lat.mean_field(e0d, mud, niters, 1.3, tile_kernel=True).cpu().numpy()
     assert native._native.lib().pl_debug_tc_timeouts() == 0
     scale = np.abs(e).max()
-    for got in (fused, unfused, flat, cuda_core):
+    for got in (fused, unfused, flat, cuda_core, tile):
         assert np.abs(got - e).max() / scale < 2e-4
         assert (got.argmin(1) == e.argmin(1)).mean() > 0.999
