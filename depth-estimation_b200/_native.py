@@ -30,6 +30,8 @@ _SIGNATURES = {
     # name: (restype, argtypes)
     "pl_lattice_create": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_uint32, C.c_void_p,
                                     C.POINTER(C.c_void_p)]),
+    "pl_lattice_create_ijrgb": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float,
+                                          C.c_uint32, C.c_void_p, C.POINTER(C.c_void_p)]),
     "pl_lattice_destroy": (None, [C.c_void_p]),
     "pl_lattice_num_points": (C.c_int64, [C.c_void_p]),
     "pl_lattice_dim": (C.c_int, [C.c_void_p]),
@@ -50,6 +52,13 @@ _SIGNATURES = {
                                             C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
     "pl_meanfield": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                C.c_int, C.c_float, C.c_uint32, C.c_void_p]),
+    "pl_meanfield_depth": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_uint32,
+                                     C.c_void_p]),
+    "pl_softargmax": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_float, C.c_void_p,
+                                C.c_void_p, C.c_void_p]),
+    "pl_cost_volume": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                 C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "pl_nchw_to_nlc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_float,
                                  C.c_void_p]),
     "pl_nlc_to_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64, C.c_float,

@@ -129,6 +129,42 @@ class CRFasRNN(nn.Module):
             Q = F.softmax(-E, dim=1)
         return -E
 
+    def depth(self, refs, logits, confidence=None, labels=None):
+        """``logits2average_depth(self(refs, logits, confidence, labels), labels)``
+        (mb_stereo_crf.py:62-66 on :93-104) -> ``[B, 1, H, W]``.  Without autograd the read-out
+        is fused into the last slice of the mean-field loop (``pl_meanfield_depth``): the final
+        logits are never written."""
+        if confidence is None:
+            confidence = 1
+        needs_grad = torch.is_grad_enabled() and (
+            logits.requires_grad or refs.requires_grad or
+            any(p.requires_grad for p in self.Mu.parameters()) or
+            (torch.is_tensor(confidence) and confidence.requires_grad))
+        if not (self.fused and not needs_grad and isinstance(self.Mu, charb) and self.niters > 0):
+            out = self.forward(refs, logits, confidence if torch.is_tensor(confidence) else None, labels)
+            probs = F.softmax(out, dim=1)
+            lab = (torch.arange(out.shape[1], dtype=torch.float32, device=out.device)
+                   if labels is None else labels.reshape(-1).to(out.device))
+            return (probs * lab[None, :, None, None]).sum(1)[:, None]
+        E0 = -logits * confidence
+        B, L, H, W = E0.shape
+        n, d = H * W, refs.shape[1]
+        dev = E0.device
+        with torch.no_grad():
+            mu, scale = self._compat_cached(L, labels, dev)
+            flat_refs = _cached(
+                refs, lambda: refs.reshape(B, d, -1).permute(0, 2, 1).contiguous())
+            E0c = E0.float().contiguous()
+            e0_nl = torch.empty((B, n, L), dtype=torch.float32, device=dev)
+            with torch.cuda.device(dev):
+                N.check(N.lib().pl_nchw_to_nlc(C.c_void_p(E0c.data_ptr()),
+                                               C.c_void_p(e0_nl.data_ptr()), B, L, n, 1.0,
+                                               N.stream_ptr(dev)))
+            lab = None if labels is None else labels.reshape(-1).float().to(dev).contiguous()
+            maps = [lattice_for(flat_refs[b]).mean_field_depth(e0_nl[b], mu, self.niters, scale,
+                                                               labels=lab)[0] for b in range(B)]
+        return torch.stack(maps).view(B, 1, H, W)
+
     def _compat_cached(self, L, labels, dev):
         """(Mu matrix on the device, exp(s) as a host float), recomputed only when gamma / s /
         labels change -- reading exp(s) back costs a host-device synchronisation per call."""
@@ -194,3 +230,36 @@ class ijGuide(nn.Module):
         ij = torch.from_numpy(np.tile(np.mgrid[:h, :w] / np.sqrt(h ** 2 + w ** 2),
                                       (bs, 1, 1, 1))).float().to(x.device)
         return ij / self.s_ij
+
+
+def stereo_pair_depth(left, right, niters=5, gamma=.05, s=0., s_ij=.1, s_rgb=.1, window_size=9,
+                      max_disp=None, criterion=None, labels=None, return_label=False):
+    """Inference pipeline of the stereo notebooks with every stage on the GPU and nothing but the
+    two images going in and the depth map coming out:
+
+      cost volume   crf/depth.py:34-53 (``disparity_badness``, ``max_disp = w // 6``)  pl_cost_volume
+      guide         crf_module.py:106-114 (``ijrgbGuide``), fused into the lattice build
+      mean field    crf_module.py:93-104 with ``Mu = charb(gamma)``, ``exp(s)`` scale     pl_meanfield
+      read-out      mb_stereo_crf.py:62-66 soft-argmax (or the arg-min label), fused into the last slice
+
+    ``left`` / ``right``: CUDA fp32 ``[h, w, 3]`` in [0, 1] (the reference's ``read_image`` layout).
+    Returns depth ``[h, w]`` (and the label map ``[h, w]`` int32 with ``return_label``).
+    """
+    import math
+    from ..lattice import PermutohedralLattice
+    from .depth import AD, cost_volume
+    N.require_cuda_f32(left, "left", 3)
+    h, w = int(left.shape[0]), int(left.shape[1])
+    L = int(max_disp) if max_disp is not None else w // 6
+    vol = cost_volume(left, right, L, window_size, criterion if criterion is not None else AD)
+    lab = None if labels is None else labels.reshape(-1).float().contiguous()
+    arange = torch.arange(L, dtype=torch.float32, device=left.device) if lab is None else lab
+    mu = charbonneir(arange[None, :], arange[:, None], gamma).contiguous()
+    lat = PermutohedralLattice.from_rgb(left.permute(2, 0, 1).contiguous(), s_ij, s_rgb)
+    try:
+        depth, label = lat.mean_field_depth(vol.view(h * w, L), mu, niters, math.exp(s), labels=lab,
+                                            want_label=return_label)
+    finally:
+        lat.close()
+    depth = depth.view(h, w)
+    return (depth, label.view(h, w)) if return_label else depth

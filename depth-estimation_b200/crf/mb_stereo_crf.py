@@ -37,8 +37,7 @@ class CRFdepthRefiner(nn.Module):
         logits, imgrgb, features = inputs
         projected_features = self.projection(features)
         guide = torch.cat((imgrgb, projected_features), dim=1)
-        filtered_logits = self.CRF(guide, logits)
-        return logits2average_depth(filtered_logits)
+        return self.CRF.depth(guide, logits)      # = logits2average_depth(self.CRF(guide, logits))
 
 
 class _CoordConv2d(nn.Module):
@@ -74,8 +73,7 @@ class CRFwUncertainty(CRFdepthRefiner):
         guide = torch.cat((imgrgb, projected_features), dim=1)
         s = self.uncertainty_net(imgrgb)
         confidence = torch.exp(-s)
-        filtered_logits = self.CRF(guide, logits, confidence)
-        depth_out = logits2average_depth(filtered_logits)
+        depth_out = self.CRF.depth(guide, logits, confidence)
         return depth_out, confidence
 
 
@@ -96,5 +94,4 @@ class CRFdepthUpsampler(nn.Module):
         logits = -10 * self.CRF.Mu.get_energies_from_scalar(upsampled_disp,
                                                             labels[None, :, None, None])
         confidence = (upsampled_disp > 1e-2).float()
-        filtered_logits = self.CRF(guide, logits, confidence=confidence, labels=labels)
-        return logits2average_depth(filtered_logits, labels[None, :, None, None])
+        return self.CRF.depth(guide, logits, confidence=confidence, labels=labels)

@@ -178,6 +178,38 @@ int pl_lattice_create(const float* ref_dev, int64_t n, int d, uint32_t flags, vo
   return PL_OK;
 }
 
+int pl_lattice_create_ijrgb(const float* rgb_planes_dev, int h, int w, float s_ij, float s_rgb,
+                            uint32_t flags, void* stream, pl_lattice** out) {
+  if (out == nullptr) return PL_ERR_INVALID;
+  *out = nullptr;
+  if (rgb_planes_dev == nullptr || h <= 0 || w <= 0 || !(s_ij != 0.f) || !(s_rgb != 0.f)) {
+    pl::set_last_error("pl_lattice_create_ijrgb: bad arguments (h=%d, w=%d)", h, w);
+    return PL_ERR_INVALID;
+  }
+  if (flags & PL_BUILD_REF_GROW_QUIRK) {
+    pl::set_last_error("PL_BUILD_REF_GROW_QUIRK is not implemented yet");
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  cudaStream_t st = (cudaStream_t)stream;
+  Lattice* L = new (std::nothrow) Lattice();
+  if (!L) return PL_ERR_INVALID;
+  L->n = (int64_t)h * w;
+  L->d = 5;
+  L->flags = flags;
+  cudaGetDevice(&L->device);
+  pl::GuideSrc gs;
+  gs.rgb = rgb_planes_dev; gs.h = h; gs.w = w; gs.s_ij = s_ij; gs.s_rgb = s_rgb;
+  gs.diag = sqrt((double)((int64_t)h * h + (int64_t)w * w));   // np.sqrt(h**2 + w**2)
+  int r = pl::lattice_build(L, nullptr, st, &gs);
+  if (r != PL_OK) {
+    pl::lattice_release(L, st);
+    return r;
+  }
+  *out = reinterpret_cast<pl_lattice*>(L);
+  return PL_OK;
+}
+
 void pl_lattice_destroy(pl_lattice* lat) {
   if (lat) pl::lattice_release(reinterpret_cast<Lattice*>(lat), (cudaStream_t)0);
 }
@@ -297,8 +329,17 @@ int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, fl
   return pl_softmax_compat_ex(e_dev, muT_dev, p_dev, q_out_dev, n, L, scale, 0u, stream);
 }
 
-int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, float* e_out_dev,
-                 float* work_dev, int L, int niters, float scale, uint32_t flags, void* stream) {
+// Read-out request of pl_meanfield_depth (all null: plain pl_meanfield, E goes to e_out_dev).
+struct Readout {
+  float* depth = nullptr;
+  int32_t* label = nullptr;
+  const float* labels = nullptr;
+  bool on() const { return depth != nullptr || label != nullptr; }
+};
+
+static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT_dev, float* e_out_dev,
+                          float* work_dev, int L, int niters, float scale, uint32_t flags,
+                          void* stream, const Readout& ro) {
   if (lat == nullptr || e0_dev == nullptr || muT_dev == nullptr || e_out_dev == nullptr ||
       work_dev == nullptr || L <= 0 || niters < 0 || e_out_dev == e0_dev) {
     pl::set_last_error("pl_meanfield: bad arguments");
@@ -354,7 +395,12 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
     pl::dev_free(mu_canon, st);
     // E = E0 + (slice - P) of the last iteration (crf_module.py:101,103)
     const float denom = 1 + powf(2, -Lt->d);
-    return pl::slice_tiled(Lt, res, L, denom, e_out_dev, L, work_dev, L, e0_dev, L, false, st);
+    if (ro.on() && pl::readout_tiled_supported(Lt, L))
+      return pl::readout_tiled(Lt, res, L, denom, work_dev, e0_dev, ro.labels, ro.depth, ro.label, st);
+    PL_TRY(pl::slice_tiled(Lt, res, L, denom, e_out_dev, L, work_dev, L, e0_dev, L, false, st));
+    if (ro.on())
+      return pl::softargmax_rows(e_out_dev, n, L, ro.labels, 1.0f, ro.depth, ro.label, st);
+    return PL_OK;
   }
   for (int it = 0; it < niters; it++) {
     // P = scale * Mu softmax(-E)          crf_module.py:99-100,102 with :71-75
@@ -363,7 +409,67 @@ int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, flo
     // E = E0 + (filter(P) - P)            crf_module.py:101 with gaussian_matrix.py:350-352
     PL_TRY(pl::lattice_apply(Lt, work_dev, L, e_out_dev, L, L, work_dev, L, e0_dev, L, flags, st));
   }
+  if (ro.on()) return pl::softargmax_rows(e_out_dev, n, L, ro.labels, 1.0f, ro.depth, ro.label, st);
   return PL_OK;
+}
+
+int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, float* e_out_dev,
+                 float* work_dev, int L, int niters, float scale, uint32_t flags, void* stream) {
+  return meanfield_impl(lat, e0_dev, muT_dev, e_out_dev, work_dev, L, niters, scale, flags, stream,
+                        Readout());
+}
+
+int pl_meanfield_depth(pl_lattice* lat, const float* e0_dev, const float* muT_dev,
+                       float* depth_out_dev, int32_t* label_out_dev, float* work_dev,
+                       const float* labels_dev, int L, int niters, float scale, uint32_t flags,
+                       void* stream) {
+  if (lat == nullptr || (depth_out_dev == nullptr && label_out_dev == nullptr) || L <= 0) {
+    pl::set_last_error("pl_meanfield_depth: bad arguments");
+    return PL_ERR_INVALID;
+  }
+  Lattice* Lt = reinterpret_cast<Lattice*>(lat);
+  cudaStream_t st = (cudaStream_t)stream;
+  Readout ro;
+  ro.depth = depth_out_dev; ro.label = label_out_dev; ro.labels = labels_dev;
+  // The fused read-out needs no E buffer; the other paths (niters == 0, label counts or flags
+  // the fused iteration does not take) write E to a temporary first.
+  const bool aligned = (((uintptr_t)e0_dev | (uintptr_t)work_dev | (uintptr_t)muT_dev) & 15u) == 0;
+  const bool fused = niters > 0 && aligned &&
+                     !(flags & (PL_APPLY_FLAT_KERNELS | PL_APPLY_EXACT_SLICE | PL_MEANFIELD_UNFUSED)) &&
+                     ((!(flags & PL_MEANFIELD_NO_TENSOR) && pl::mf_tc_supported(Lt, L)) ||
+                      pl::mf_fused_supported(Lt, L)) &&
+                     pl::readout_tiled_supported(Lt, L);
+  if (fused)   // e_out is never written on this path: any non-null pointer distinct from e0
+    return meanfield_impl(lat, e0_dev, muT_dev, work_dev, work_dev, L, niters, scale, flags, stream, ro);
+  float* e_tmp = nullptr;
+  PL_TRY(pl::dev_alloc((void**)&e_tmp, sizeof(float) * (size_t)Lt->n * L, st));
+  int r = meanfield_impl(lat, e0_dev, muT_dev, e_tmp, work_dev, L, niters, scale, flags, stream, ro);
+  if (r == PL_OK && niters == 0)
+    r = pl::softargmax_rows(e_tmp, Lt->n, L, labels_dev, 1.0f, depth_out_dev, label_out_dev, st);
+  pl::dev_free(e_tmp, st);
+  return r;
+}
+
+int pl_softargmax(const float* rows_dev, int64_t n, int L, const float* labels_dev, float sign,
+                  float* depth_out_dev, int32_t* label_out_dev, void* stream) {
+  if (rows_dev == nullptr || n < 0 || L <= 0 || (depth_out_dev == nullptr && label_out_dev == nullptr)) {
+    pl::set_last_error("pl_softargmax: bad arguments");
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  return pl::softargmax_rows(rows_dev, n, L, labels_dev, sign, depth_out_dev, label_out_dev,
+                             (cudaStream_t)stream);
+}
+
+int pl_cost_volume(const float* left_dev, const float* right_dev, float* out_dev, int h, int w,
+                   int channels, int max_disp, int window, int criterion, void* stream) {
+  if (left_dev == nullptr || right_dev == nullptr || out_dev == nullptr) {
+    pl::set_last_error("pl_cost_volume: null pointer");
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  return pl::cost_volume(left_dev, right_dev, out_dev, h, w, channels, max_disp, window, criterion,
+                         (cudaStream_t)stream);
 }
 
 int pl_nchw_to_nlc(const float* src_dev, float* dst_dev, int64_t batch, int C, int64_t n,

@@ -75,7 +75,7 @@ __device__ __forceinline__ void load_key(const int16_t* __restrict__ greedy,
 // ---------------------------------------------------------------------------
 template <int D>
 __global__ void __launch_bounds__(256)
-elevate_kernel(const float* __restrict__ ref, int64_t n, ScaleFactors sf,
+elevate_kernel(const float* __restrict__ ref, const GuideSrc gs, int64_t n, ScaleFactors sf,
                int16_t* __restrict__ greedy_out, int8_t* __restrict__ rank_out,
                float* __restrict__ bary_out) {
   constexpr int D1 = D + 1;
@@ -83,8 +83,21 @@ elevate_kernel(const float* __restrict__ ref, int64_t n, ScaleFactors sf,
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n;
        p += (int64_t)gridDim.x * blockDim.x) {
     float pos[D];
+    if (D == 5 && gs.rgb != nullptr) {
+      // ijrgbGuide.forward (crf_module.py:111-114) evaluated in place: ij = mgrid / sqrt(h^2+w^2)
+      // in float64, cast to fp32, then fp32 divisions by s_ij / s_rgb -- bit for bit what torch
+      // computes, so the [n, 5] feature matrix never exists in HBM.
+      const int y = (int)(p / gs.w), x = (int)(p - (int64_t)y * gs.w);
+      const int64_t hw = (int64_t)gs.h * gs.w;
+      pos[0] = __fdiv_rn(__double2float_rn((double)y / gs.diag), gs.s_ij);
+      pos[1 % D] = __fdiv_rn(__double2float_rn((double)x / gs.diag), gs.s_ij);
+      pos[2 % D] = __fdiv_rn(gs.rgb[p], gs.s_rgb);
+      pos[3 % D] = __fdiv_rn(gs.rgb[hw + p], gs.s_rgb);
+      pos[4 % D] = __fdiv_rn(gs.rgb[2 * hw + p], gs.s_rgb);
+    } else {
 #pragma unroll
-    for (int i = 0; i < D; i++) pos[i] = ref[p * D + i];
+      for (int i = 0; i < D; i++) pos[i] = ref[p * D + i];
+    }
 
     // :380-384  (int * float) * float, left to right; a - b + c left to right
     float el[D1];
@@ -461,7 +474,7 @@ uint64_t pow2_ceil(uint64_t x) {
 }
 
 template <int D>
-int build_impl(Lattice* L, const float* ref, cudaStream_t st) {
+int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st) {
   constexpr int D1 = D + 1;
   const int64_t n = L->n;
   const uint64_t E = (uint64_t)n * D1;
@@ -478,7 +491,7 @@ int build_impl(Lattice* L, const float* ref, cudaStream_t st) {
   ScaleFactors sf;
   for (int i = 0; i < PL_MAX_D; i++) sf.s[i] = 0.f;
   reference_scale_factors(D, sf.s);
-  PL_LAUNCH((elevate_kernel<D>), grid_for((uint64_t)n, 256, 8), 256, 0, st, ref, n, sf, L->greedy,
+  PL_LAUNCH((elevate_kernel<D>), grid_for((uint64_t)n, 256, 8), 256, 0, st, ref, gs, n, sf, L->greedy,
             L->rank, L->bary);
 
   const uint32_t nchunks = ceil_div_u(E, kScanChunk);
@@ -538,11 +551,13 @@ int build_impl(Lattice* L, const float* ref, cudaStream_t st) {
 
 }  // namespace
 
-int lattice_build(Lattice* L, const float* ref, cudaStream_t st) {
+int lattice_build(Lattice* L, const float* ref, cudaStream_t st, const GuideSrc* guide) {
+  GuideSrc gs;
+  if (guide != nullptr) gs = *guide;
   switch (L->d) {
 #define PL_CASE(DD) \
   case DD:          \
-    return build_impl<DD>(L, ref, st);
+    return build_impl<DD>(L, ref, gs, st);
     PL_CASE(1) PL_CASE(2) PL_CASE(3) PL_CASE(4) PL_CASE(5) PL_CASE(6) PL_CASE(7) PL_CASE(8)
     PL_CASE(9) PL_CASE(10) PL_CASE(11) PL_CASE(12) PL_CASE(13) PL_CASE(14) PL_CASE(15) PL_CASE(16)
 #undef PL_CASE

@@ -91,8 +91,15 @@ struct Lattice {
   int64_t bytes = 0;         // persistent device bytes
 };
 
-// build (pl_build.cu)
-int lattice_build(Lattice* L, const float* ref, cudaStream_t st);
+// build (pl_build.cu).  With `guide` (d = 5) the features are evaluated inside the elevation
+// kernel from the RGB planes (ijrgbGuide, crf_module.py:106-114) and `ref` is not read.
+struct GuideSrc {
+  const float* rgb = nullptr;  // [3][h][w] planes of one image
+  int h = 0, w = 0;
+  float s_ij = 1.f, s_rgb = 1.f;
+  double diag = 1.0;           // sqrt(h^2 + w^2) in float64, as numpy computes it
+};
+int lattice_build(Lattice* L, const float* ref, cudaStream_t st, const GuideSrc* guide = nullptr);
 // tile-local view + tiled kernels (pl_tiles.cu)
 int lattice_build_tiles(Lattice* L, cudaStream_t st);
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
@@ -142,6 +149,16 @@ int nchw_to_nlc(const float* src, float* dst, int64_t batch, int C, int64_t n, f
                 cudaStream_t st);
 int nlc_to_nchw(const float* src, float* dst, int64_t batch, int C, int64_t n, float alpha,
                 cudaStream_t st);
+
+// matching cost volume (pl_cost.cu) and fused depth read-out (pl_readout.cu)
+int cost_volume(const float* im1, const float* im2, float* out, int h, int w, int ch, int L, int ws,
+                int criterion, cudaStream_t st);
+bool readout_tiled_supported(const Lattice* L, int labels);
+int readout_tiled(Lattice* L, const float* val, int labels, float denom, const float* p,
+                  const float* e0, const float* label_values, float* depth, int* label_out,
+                  cudaStream_t st);
+int softargmax_rows(const float* e, int64_t n, int labels, const float* label_values, float sign,
+                    float* depth, int* label_out, cudaStream_t st);
 
 // stream-ordered allocation helpers (pl_api.cu)
 int dev_alloc(void** p, size_t bytes, cudaStream_t st);

@@ -1,0 +1,204 @@
+// pl_readout.cu -- last slice of the mean-field loop fused with the depth readout (sm_100a).
+//
+// Inference wants a depth map, not the [n][L] energies: crf/mb_stereo_crf.py:62-66
+// (`logits2average_depth`: sum_l softmax(logits)_l * label_l with logits = -E) and the
+// notebooks' argmax read-out (Experiments/trainableDenseCRF.ipynb cell 8).  readout_tiled_kernel
+// does the final  E = E0 + slice(blurred lattice) / (1 + 2^-d) - P  (crf_module.py:101,103) per
+// pixel in registers and reduces it on the spot, so the last E (4 n L bytes written and read
+// again by torch's softmax) never reaches HBM: reads 8 n L + lists, writes 4 n (+ 4 n).
+//
+// softargmax_rows_kernel is the same reduction over energies already in HBM (any L): the
+// fall-back behind pl_meanfield_depth for label counts the tiled kernel does not take, and
+// the pixel-major form of logits2average_depth.
+#include <math.h>
+
+#include "pl_common.cuh"
+
+namespace pl {
+
+namespace {
+
+constexpr int kTile = PL_TILE;
+constexpr int kThreads = 256;
+constexpr int kStageBytes = 64 * 1024;
+
+struct Red {
+  float m, s, t;   // running max of -e, sum of exp, sum of exp * label
+  float best;      // smallest energy and its label index (first on ties)
+  int arg;
+};
+
+__device__ __forceinline__ void red_init(Red& r) {
+  r.m = -INFINITY; r.s = 0.f; r.t = 0.f; r.best = INFINITY; r.arg = 0x7fffffff;
+}
+// online softmax update with one element
+__device__ __forceinline__ void red_push(Red& r, float e, float label, int idx) {
+  const float x = -e;
+  if (x > r.m) {
+    const float c = __expf(r.m - x);
+    r.s = r.s * c + 1.f;
+    r.t = r.t * c + label;
+    r.m = x;
+  } else {
+    const float p = __expf(x - r.m);
+    r.s += p;
+    r.t = fmaf(p, label, r.t);
+  }
+  if (e < r.best || (e == r.best && idx < r.arg)) { r.best = e; r.arg = idx; }
+}
+__device__ __forceinline__ void red_merge(Red& a, float m, float s, float t, float best, int arg) {
+  const float M = fmaxf(a.m, m);
+  const float ca = (a.m == -INFINITY) ? 0.f : __expf(a.m - M);
+  const float cb = (m == -INFINITY) ? 0.f : __expf(m - M);
+  a.s = a.s * ca + s * cb;
+  a.t = a.t * ca + t * cb;
+  a.m = M;
+  if (best < a.best || (best == a.best && arg < a.arg)) { a.best = best; a.arg = arg; }
+}
+__device__ __forceinline__ void red_group(Red& r, int G) {
+  for (int o = G >> 1; o > 0; o >>= 1) {
+    const float m = __shfl_xor_sync(0xffffffffu, r.m, o, G);
+    const float s = __shfl_xor_sync(0xffffffffu, r.s, o, G);
+    const float t = __shfl_xor_sync(0xffffffffu, r.t, o, G);
+    const float b = __shfl_xor_sync(0xffffffffu, r.best, o, G);
+    const int a = __shfl_xor_sync(0xffffffffu, r.arg, o, G);
+    red_merge(r, m, s, t, b, a);
+  }
+}
+
+// One CTA per tile of 128 pixels; G lanes per pixel (power of two, <= 32), each lane owns the
+// float4 columns lane, lane + G, ... of the pixel's L labels.
+__global__ void __launch_bounds__(kThreads)
+readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
+                     const uint16_t* __restrict__ loc, const float* __restrict__ bary,
+                     const int32_t* __restrict__ vid, const int2* __restrict__ useg,
+                     const int* __restrict__ tile_off, const int* __restrict__ tile_U,
+                     float inv_denom, const float* __restrict__ p, const float* __restrict__ e0,
+                     const float* __restrict__ labels, float* __restrict__ depth,
+                     int* __restrict__ label_out, int G) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int TE = kTile * d1;
+  float* s_w = reinterpret_cast<float*>(smem_raw);          // [TE]
+  int* s_idx = reinterpret_cast<int*>(s_w + TE);            // [TE]
+  float* s_lab = reinterpret_cast<float*>(s_idx + TE);      // [L]
+  float* s_val = s_lab + ((L + 3) & ~3);                    // [U][L] when staged
+
+  const int tid = threadIdx.x;
+  const int64_t tile = blockIdx.x;
+  const int64_t p0 = tile * kTile;
+  const int rows = (int)min((int64_t)kTile, n - p0);
+  const int U = tile_U[tile];
+  const int V = L >> 2;
+  const bool staged = (size_t)U * L * 4 <= (size_t)kStageBytes;
+
+  if (staged) {
+    const int2* seg = useg + tile_off[tile];
+    for (int i = tid; i < U * V; i += kThreads) {
+      const int u = i / V, v = i - u * V;
+      *reinterpret_cast<float4*>(s_val + u * L + 4 * v) =
+          *reinterpret_cast<const float4*>(val + (int64_t)seg[u].x * L + 4 * v);
+    }
+  }
+  const int valid = rows * d1;
+  for (int i = tid; i < valid; i += kThreads) {
+    s_w[i] = bary[tile * TE + i] * inv_denom;
+    s_idx[i] = staged ? (int)loc[tile * TE + i] : vid[tile * TE + i];
+  }
+  for (int i = tid; i < L; i += kThreads) s_lab[i] = labels ? labels[i] : (float)i;
+  __syncthreads();
+
+  const int g = tid / G, l = tid % G, groups = kThreads / G;
+  for (int r = g; r < rows; r += groups) {
+    const int64_t px = p0 + r;
+    Red red;
+    red_init(red);
+    for (int v = l; v < V; v += G) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < d1; j++) {
+        const float w = s_w[r * d1 + j];
+        const int ix = s_idx[r * d1 + j];
+        const float4 x = staged ? *reinterpret_cast<const float4*>(s_val + ix * L + 4 * v)
+                                : *reinterpret_cast<const float4*>(val + (int64_t)ix * L + 4 * v);
+        acc.x = __fmaf_rn(w, x.x, acc.x);
+        acc.y = __fmaf_rn(w, x.y, acc.y);
+        acc.z = __fmaf_rn(w, x.z, acc.z);
+        acc.w = __fmaf_rn(w, x.w, acc.w);
+      }
+      const float4 pp = *reinterpret_cast<const float4*>(p + px * L + 4 * v);
+      const float4 ee = *reinterpret_cast<const float4*>(e0 + px * L + 4 * v);
+      const float4 lb = *reinterpret_cast<const float4*>(s_lab + 4 * v);
+      red_push(red, __fadd_rn(ee.x, __fsub_rn(acc.x, pp.x)), lb.x, 4 * v);
+      red_push(red, __fadd_rn(ee.y, __fsub_rn(acc.y, pp.y)), lb.y, 4 * v + 1);
+      red_push(red, __fadd_rn(ee.z, __fsub_rn(acc.z, pp.z)), lb.z, 4 * v + 2);
+      red_push(red, __fadd_rn(ee.w, __fsub_rn(acc.w, pp.w)), lb.w, 4 * v + 3);
+    }
+    red_group(red, G);
+    if (l == 0) {
+      if (depth) depth[px] = red.t / red.s;
+      if (label_out) label_out[px] = red.arg;
+    }
+  }
+}
+
+// energies already in HBM: one warp per row, any L
+__global__ void __launch_bounds__(kThreads)
+softargmax_rows_kernel(const float* __restrict__ e, int64_t n, int L,
+                       const float* __restrict__ labels, float sign, float* __restrict__ depth,
+                       int* __restrict__ label_out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (int64_t)gridDim.x * (kThreads / 32);
+  for (int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5); row < n; row += warps) {
+    Red red;
+    red_init(red);
+    for (int i = lane; i < L; i += 32)
+      red_push(red, sign * e[row * L + i], labels ? labels[i] : (float)i, i);
+    red_group(red, 32);
+    if (lane == 0) {
+      if (depth) depth[row] = red.t / red.s;
+      if (label_out) label_out[row] = red.arg;
+    }
+  }
+}
+
+}  // namespace
+
+bool readout_tiled_supported(const Lattice* L, int labels) {
+  return L != nullptr && L->ntiles > 0 && L->loc != nullptr && (labels & 3) == 0 && labels >= 4;
+}
+
+// depth / label_out from the blurred lattice `val` of the last iteration, P and E0
+int readout_tiled(Lattice* L, const float* val, int labels, float denom, const float* p,
+                  const float* e0, const float* label_values, float* depth, int* label_out,
+                  cudaStream_t st) {
+  const int d1 = L->d + 1;
+  const int TE = kTile * d1;
+  int G = 1;
+  while (G < 32 && G < labels / 4) G <<= 1;
+  const size_t smem = sizeof(float) * (size_t)(2 * TE + ((labels + 3) & ~3)) + kStageBytes;
+  static bool attr_done = false;
+  if (!attr_done) {
+    PL_CUDA(cudaFuncSetAttribute(readout_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 100 * 1024));
+    attr_done = true;
+  }
+  if (smem > 100 * 1024) {
+    set_last_error("readout_tiled: d + 1 = %d too large", d1);
+    return PL_ERR_INVALID;
+  }
+  PL_LAUNCH(readout_tiled_kernel, (unsigned)L->ntiles, kThreads, smem, st, val, labels, L->n, d1,
+            L->loc, L->bary, L->vid, L->useg, L->tile_off, L->tile_U, 1.0f / denom, p, e0,
+            label_values, depth, label_out, G);
+  return PL_OK;
+}
+
+// sign = +1: rows are energies E (soft-argmax of softmax(-E));  sign = -1: rows are logits
+int softargmax_rows(const float* e, int64_t n, int labels, const float* label_values, float sign,
+                    float* depth, int* label_out, cudaStream_t st) {
+  if (n <= 0) return PL_OK;
+  const unsigned grid = grid_for((uint64_t)n * 32, kThreads, 8);
+  PL_LAUNCH(softargmax_rows_kernel, grid, kThreads, 0, st, e, n, labels, label_values, sign, depth,
+            label_out);
+  return PL_OK;
+}
+
+}  // namespace pl

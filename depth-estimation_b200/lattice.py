@@ -39,6 +39,27 @@ class PermutohedralLattice:
                                               N.stream_ptr(self.device), C.byref(self._h)))
         self.num_vertices = int(N.lib().pl_lattice_num_vertices(self._h))
 
+    @classmethod
+    def from_rgb(cls, rgb, s_ij=0.1, s_rgb=0.1):
+        """Lattice of ``ijrgbGuide(s_ij, s_rgb)(rgb[None])`` (crf_module.py:106-114) for one image
+        ``rgb[3, h, w]``: the features are evaluated inside the elevation kernel, bit for bit
+        what the module computes, and never written to memory."""
+        N.require_cuda_f32(rgb, "rgb", 3)
+        if rgb.shape[0] != 3:
+            raise ValueError(f"rgb must be [3, h, w], got {tuple(rgb.shape)}")
+        rgb = rgb.contiguous()
+        self = cls.__new__(cls)
+        self.device = rgb.device
+        h, w = int(rgb.shape[1]), int(rgb.shape[2])
+        self.n, self.d = h * w, 5
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            N.check(N.lib().pl_lattice_create_ijrgb(
+                C.c_void_p(rgb.data_ptr()), h, w, float(s_ij), float(s_rgb), N.PL_BUILD_DEFAULT,
+                N.stream_ptr(self.device), C.byref(self._h)))
+        self.num_vertices = int(N.lib().pl_lattice_num_vertices(self._h))
+        return self
+
     # -- value path ---------------------------------------------------------
     def filter(self, src, sub=None, add=None, exact_slice=False, out=None, flat=False):
         """``filter(src) - sub + add`` for ``src[n, C]`` (row stride may exceed C).
@@ -103,6 +124,38 @@ class PermutohedralLattice:
                 C.c_void_p(out.data_ptr()), C.c_void_p(work.data_ptr()), L, int(niters),
                 float(scale), flags, N.stream_ptr(self.device)))
         return out
+
+    def mean_field_depth(self, e0, mu, niters, scale=1.0, labels=None, want_depth=True,
+                         want_label=False, unfused=False, no_tensor=False, tile_kernel=False):
+        """``mean_field`` followed by the read-out, fused into the last slice: soft-argmax depth
+        ``sum_l softmax(-E)_l * labels[l]`` (mb_stereo_crf.py:62-66) and / or the arg-min label.
+        Returns ``(depth[n] or None, label[n] int32 or None)``; E itself is not materialised."""
+        self._check_rows(e0, "e0")
+        e0 = e0.contiguous()
+        L = int(e0.shape[1])
+        N.require_cuda_f32(mu, "mu", 2)
+        if tuple(mu.shape) != (L, L):
+            raise ValueError(f"mu must be [{L}, {L}]")
+        mu_t = mu.t().contiguous()
+        if labels is not None:
+            N.require_cuda_f32(labels, "labels")
+            labels = labels.reshape(-1).contiguous()
+            if labels.numel() != L:
+                raise ValueError(f"labels must have {L} entries")
+        depth = torch.empty((self.n,), dtype=torch.float32, device=self.device) if want_depth else None
+        label = torch.empty((self.n,), dtype=torch.int32, device=self.device) if want_label else None
+        if depth is None and label is None:
+            raise ValueError("nothing to read out")
+        work = torch.empty_like(e0)
+        flags = ((N.PL_MEANFIELD_UNFUSED if unfused else 0)
+                 | (N.PL_MEANFIELD_NO_TENSOR if no_tensor else 0)
+                 | (N.PL_MEANFIELD_TILE_KERNEL if tile_kernel else 0))
+        ptr = lambda t: C.c_void_p(t.data_ptr() if t is not None else 0)
+        with torch.cuda.device(self.device):
+            N.check(N.lib().pl_meanfield_depth(
+                self._h, ptr(e0), ptr(mu_t), ptr(depth), ptr(label), ptr(work), ptr(labels), L,
+                int(niters), float(scale), flags, N.stream_ptr(self.device)))
+        return depth, label
 
     # -- inspection (parity tests) -------------------------------------------
     def export(self):

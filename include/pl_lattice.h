@@ -64,6 +64,13 @@ typedef struct pl_lattice pl_lattice; /* opaque */
  * Synchronises `stream` once (the vertex count has to reach the host). */
 int pl_lattice_create(const float* ref_dev, int64_t n, int d, uint32_t flags, void* stream,
                       pl_lattice** out);
+/* Same lattice from an RGB image: the features of ijrgbGuide.forward (crf_module.py:106-114),
+ *   (i / diag / s_ij, j / diag / s_ij, r / s_rgb, g / s_rgb, b / s_rgb),  diag = sqrt(h^2 + w^2)
+ * are evaluated inside the elevation kernel with the reference's rounding (float64 mgrid / diag
+ * cast to fp32, then fp32 divisions), so the [n][5] feature matrix is never materialised.
+ * rgb_planes_dev: [3][h][w] fp32 (one image of the module's NCHW input). */
+int pl_lattice_create_ijrgb(const float* rgb_planes_dev, int h, int w, float s_ij, float s_rgb,
+                            uint32_t flags, void* stream, pl_lattice** out);
 void pl_lattice_destroy(pl_lattice* lat);
 
 int64_t pl_lattice_num_points(const pl_lattice* lat);   /* n */
@@ -147,6 +154,33 @@ int pl_softmax_compat_blocked(const float* e_blocks_dev, int nblocks, const floa
  * returns -E).  work_dev: caller-provided scratch of n*L floats. */
 int pl_meanfield(pl_lattice* lat, const float* e0_dev, const float* muT_dev, float* e_out_dev,
                  float* work_dev, int L, int niters, float scale, uint32_t flags, void* stream);
+
+/* pl_meanfield followed by the depth read-out of crf/mb_stereo_crf.py:62-66
+ * (logits2average_depth: sum_l softmax(-E)_l * labels[l]) and / or the argmax label of the
+ * notebooks (Experiments/trainableDenseCRF.ipynb cell 8), fused into the last slice so the
+ * final E never reaches HBM.  depth_out_dev [n] f32 and label_out_dev [n] i32 may each be NULL;
+ * labels_dev [L] f32 or NULL for labels 0..L-1 (mb_stereo_crf.py:64).  work_dev: n*L floats. */
+int pl_meanfield_depth(pl_lattice* lat, const float* e0_dev, const float* muT_dev,
+                       float* depth_out_dev, int32_t* label_out_dev, float* work_dev,
+                       const float* labels_dev, int L, int niters, float scale, uint32_t flags,
+                       void* stream);
+/* The same read-out of rows already in HBM: rows_dev [n][L]; sign = +1 rows are energies E,
+ * sign = -1 rows are logits (softmax(logits), mb_stereo_crf.py:63). */
+int pl_softargmax(const float* rows_dev, int64_t n, int L, const float* labels_dev, float sign,
+                  float* depth_out_dev, int32_t* label_out_dev, void* stream);
+
+/* Plane-sweep matching cost volume, the unaries the CRF reads: crf/depth.py:34-53
+ * (disparity_badness).  left_dev / right_dev: [h][w][channels] fp32 (the reference's numpy image
+ * layout); out_dev: [h*w][max_disp] fp32, pixel-major -- the layout pl_meanfield consumes.
+ *   out[y][x][i] = window-sum (window x window, scipy 'reflect' boundary) of
+ *                  sum_c crit(left[y][x][c], right[y][x - i][c])   (0 where x - i < 0)
+ * criterion: 0 = AD |a-b| (depth.py:20), 1 = SD (a-b)^2 (:18), 2 = nprod -a*b (:22).
+ * window odd, <= 17.  The reference uses max_disp = w / 6 (depth.py:40). */
+#define PL_COST_AD 0
+#define PL_COST_SD 1
+#define PL_COST_NPROD 2
+int pl_cost_volume(const float* left_dev, const float* right_dev, float* out_dev, int h, int w,
+                   int channels, int max_disp, int window, int criterion, void* stream);
 
 /* Layout helpers for the module surface (NCHW tensors <-> pixel-major):
  * dst[b][p][c] = alpha * src[b][c][p]   and back. */

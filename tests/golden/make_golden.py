@@ -184,6 +184,56 @@ def main():
                             depth=rmb.logits2average_depth(lg).numpy(),
                             depth_labels=rmb.logits2average_depth(
                                 lg, torch.linspace(0, 2, 5)[None, :, None, None]).numpy())
+    # ---- 7. cost volume and fixture readers: crf/depth.py:34-53, crf/utils.py:46-109 --------
+    # crf/depth.py imports cv2.ximgproc (opencv-contrib, absent) for an unrelated guided-filter
+    # operator and crf/utils.py imports skimage for `grayscale`: both stubbed, neither is called.
+    import cv2
+    if not hasattr(cv2, "ximgproc"):
+        cv2.ximgproc = _stub("cv2.ximgproc", guidedFilter=None)
+    if "skimage" not in sys.modules:
+        sk = _stub("skimage")
+        sk.color = _stub("skimage.color", rgb2gray=None)
+    import crf.depth as rdepth
+    import crf.utils as rutils
+    left = synthetic.image(26, 44, seed=3).astype(np.float64)
+    disp = synthetic.disparity(26, 44, 44 // 6, 3)
+    right = np.zeros_like(left)
+    for y in range(26):
+        for x in range(44):
+            xs = x + int(disp[y, x])
+            if xs < 44:
+                right[y, x] = left[y, xs]
+    np.savez_compressed(os.path.join(HERE, "cost_volume_26x44.npz"), left=left, right=right,
+                        ad9=rdepth.disparity_badness(left, right),
+                        sd5=rdepth.disparity_badness(left, right, 5, rdepth.SD),
+                        np3=rdepth.disparity_badness(left, right, 3, rdepth.nprod),
+                        est=rdepth.disparity_estimate(left, right))
+    import tempfile
+    rng = np.random.default_rng(4)
+    with tempfile.TemporaryDirectory() as tmp:
+        gray = rng.integers(0, 256, (9, 13), dtype=np.uint8)
+        pgm = b"P5\n# synthetic ground truth\n13 9\n255\n" + gray.tobytes()
+        with open(os.path.join(tmp, "a.pgm"), "wb") as f:
+            f.write(pgm)
+        pf = rng.random((7, 11)).astype("<f4")
+        pfm_le = b"Pf\n11 7\n-1.0\n" + pf.tobytes()
+        pfm_be = b"Pf\n11 7\n1.0\n" + pf.astype(">f4").tobytes()
+        for name, blob in (("le.pfm", pfm_le), ("be.pfm", pfm_be)):
+            with open(os.path.join(tmp, name), "wb") as f:
+                f.write(blob)
+        from PIL import Image
+        rgb8 = rng.integers(0, 256, (6, 8, 3), dtype=np.uint8)
+        Image.fromarray(rgb8).save(os.path.join(tmp, "c.png"))
+        with open(os.path.join(tmp, "c.png"), "rb") as f:
+            png = f.read()
+        np.savez_compressed(os.path.join(HERE, "fixture_readers.npz"),
+                            pgm_bytes=np.frombuffer(pgm, np.uint8), pgm=rutils.read_pgm(os.path.join(tmp, "a.pgm")),
+                            pfm_le_bytes=np.frombuffer(pfm_le, np.uint8),
+                            pfm_le=rutils.read_pfm(os.path.join(tmp, "le.pfm")),
+                            pfm_be_bytes=np.frombuffer(pfm_be, np.uint8),
+                            pfm_be=rutils.read_pfm(os.path.join(tmp, "be.pfm")),
+                            png_bytes=np.frombuffer(png, np.uint8),
+                            png=rutils.read_image(os.path.join(tmp, "c.png")))
     print("golden vectors written to", HERE)
 
 

@@ -73,3 +73,38 @@ def test_oracle_stereo_readout_matches_reference_golden():
     np.testing.assert_allclose(O.logits2average_depth(lg).numpy(), z["depth"], atol=1e-6)
     lab = torch.linspace(0, 2, 5)[None, :, None, None]
     np.testing.assert_allclose(O.logits2average_depth(lg, lab).numpy(), z["depth_labels"], atol=1e-6)
+
+
+def test_depth_oracle_matches_reference_cost_volume_golden():
+    """oracle/depth_oracle.py against crf.depth.disparity_badness itself (AD/9, SD/5, nprod/3)."""
+    from oracle import depth_oracle as D
+    z = _load("cost_volume_26x44.npz")
+    left, right = z["left"], z["right"]
+    np.testing.assert_allclose(D.disparity_badness(left, right), z["ad9"], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(D.disparity_badness(left, right, 5, D.SD), z["sd5"], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(D.disparity_badness(left, right, 3, D.nprod), z["np3"], rtol=0, atol=1e-12)
+    assert np.array_equal(D.disparity_estimate(left, right), z["est"])
+
+
+def test_fixture_readers_match_reference_golden(tmp_path):
+    """crf/utils.py readers (host code of the package) on the byte streams the reference read."""
+    import importlib
+    U = importlib.import_module("depth_estimation_b200.crf.utils")
+    z = _load("fixture_readers.npz")
+    for name, reader, key in (("a.pgm", U.read_pgm, "pgm"), ("le.pfm", U.read_pfm, "pfm_le"),
+                              ("be.pfm", U.read_pfm, "pfm_be"), ("c.png", U.read_image, "png")):
+        path = tmp_path / name
+        path.write_bytes(z[key + "_bytes"].tobytes())
+        got = reader(str(path))
+        assert got.shape == z[key].shape and got.dtype == z[key].dtype, name
+        assert np.array_equal(got, z[key]), name
+    # where the reference fails: 16-bit PGM (undefined `byteorder`), colour PFM, bad header
+    wide = (np.arange(12) * 1000).astype(">u2").reshape(3, 4)
+    (tmp_path / "w.pgm").write_bytes(b"P5\n4 3\n65535\n" + wide.tobytes())
+    assert np.array_equal(U.read_pgm(str(tmp_path / "w.pgm")), wide)
+    col = np.arange(24, dtype="<f4").reshape(2, 4, 3)
+    (tmp_path / "c.pfm").write_bytes(b"PF\n4 2\n-1.0\n" + col.tobytes())
+    assert np.array_equal(U.read_pfm(str(tmp_path / "c.pfm")), np.flip(col, 0).astype(np.float64))
+    (tmp_path / "bad.pgm").write_bytes(b"P2\n1 1\n255\n0")
+    with pytest.raises(ValueError):
+        U.read_pgm(str(tmp_path / "bad.pgm"))
