@@ -306,7 +306,7 @@ def run_ours(args, rank, local_rank, world):
         with torch.no_grad():
             g = guide_h.to(dev, non_blocking=True)
             lg = logits_h.to(dev, non_blocking=True)
-            depth = mb.logits2average_depth(crf(g, lg))
+            depth = crf.depth(g, lg)      # = logits2average_depth(crf(g, lg)), read-out fused
             depth_h.copy_(depth, non_blocking=True)
             torch.cuda.synchronize(dev)
         gm.clear_lattice_cache()
@@ -346,7 +346,7 @@ def run_ours(args, rank, local_rank, world):
                         ev.record(copy_st)
                     ev.synchronize()               # inputs are on the device
                     with torch.cuda.stream(comp_st):
-                        depth = mb.logits2average_depth(crf(g_d[t], lg_d[t]))
+                        depth = crf.depth(g_d[t], lg_d[t])
                         dh[t].copy_(depth, non_blocking=True)
                     comp_st.synchronize()          # this frame's depth map is on the host
                     gm.forget(g_d[t])
@@ -373,6 +373,31 @@ def run_ours(args, rank, local_rank, world):
     e2e_s = reduce_max(time.perf_counter() - t0)
     e2e_value = world * args.steps / e2e_s
     gm.clear_lattice_cache()
+
+    # ---- extra: the stereo notebooks' whole pipeline, two images in -> depth map out ----
+    # (cost volume crf/depth.py:34-53 with max_disp = L, guide fused into the lattice build,
+    # 5 mean-field iterations, soft-argmax fused into the last slice; H2D of both images and
+    # D2H of the depth map inside the timed region)
+    left_h = torch.from_numpy(np.ascontiguousarray(img)).pin_memory()
+    right_h = torch.from_numpy(np.ascontiguousarray(np.roll(img, -5, axis=1))).pin_memory()
+    pair_depth_h = torch.empty((H, W), dtype=torch.float32).pin_memory()
+
+    def pair_step():
+        with torch.no_grad():
+            lt = left_h.to(dev, non_blocking=True)
+            rt = right_h.to(dev, non_blocking=True)
+            pair_depth_h.copy_(cm.stereo_pair_depth(lt, rt, niters=NITERS, gamma=GAMMA, max_disp=L),
+                               non_blocking=True)
+            torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        pair_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        pair_step()
+    barrier()
+    pair_value = world * args.steps / reduce_max(time.perf_counter() - t0)
 
     # ---- per-kernel durations for the roofline (separate pass, same inputs) ----
     roofline = None
@@ -430,7 +455,11 @@ def run_ours(args, rank, local_rank, world):
             "gpu_launches": int(launches) * world,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "extra": {"lattice_filter_mpix_labels_per_s_incl_build": n * L * NITERS / (ms_per_step * 1e-3) / 1e6,
-                      "vertices": state["M"]},
+                      "vertices": state["M"],
+                      "stereo_pair_to_depth_frames_per_s": pair_value,
+                      "stereo_pair_h2d_bytes_per_step": int(2 * left_h.numel() * 4),
+                      "stereo_pair_note": "images -> pl_cost_volume -> fused guide + 5 mean-field "
+                                          "iterations -> fused soft-argmax; one frame at a time"},
         }))
     if world > 1:
         dist.destroy_process_group()

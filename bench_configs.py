@@ -109,6 +109,62 @@ def filter_sweep(args, dev):
         lat.close()
 
 
+def ref_cuda_filter(args, dev):
+    """The reference's own CUDA lattice (crf/lattice/cuda_lattice, rebuilt in place for sm_100a by
+    oracle/build_ref.py) beside ours on the shapes it supports: vd = 3 value channels, pd = 5,
+    host buffers in and out (its MirroredArray copies are part of its call).  Speed only: it is
+    Adams' normalised filter, not the lite path's arithmetic."""
+    import ctypes as C
+    import time
+    import numpy as np
+    import torch
+    import depth_estimation_b200 as pkg
+    so = os.path.join(ROOT, "oracle", "_ref", "libref_cuda_lattice.so")
+    if not os.path.exists(so):
+        print(json.dumps({"workload": "ref_cuda_filter", "unavailable": "oracle/_ref/libref_cuda_lattice.so not built"}))
+        return
+    lib = C.CDLL(so)
+    lib.filter.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_bool]
+    lib.filter.restype = None
+    N = pkg._native
+    for (h, w) in ([(1024, 1024)] if args.quick else [(500, 740), (1024, 1024), (2048, 1024)]):
+        n = h * w
+        feats = _features(h, w, 1, dev).cpu().numpy()
+        src = np.random.default_rng(0).random((n, 3)).astype(np.float32)
+        # reference CUDA: filters `im` in place (host pointers)
+        t_ref = []
+        for rep in range(1 + max(1, args.steps)):
+            im = src.copy()
+            t0 = time.perf_counter()
+            lib.filter(im.ctypes.data, feats.ctypes.data, 5, 3, w, h, True)
+            torch.cuda.synchronize(dev)
+            t_ref.append(time.perf_counter() - t0)
+        t_ref = sorted(t_ref[1:])[len(t_ref[1:]) // 2]
+        # ours through the same kind of call: host buffers in, host buffer out (pl_filter_host)
+        out = np.empty_like(src)
+        t_our = []
+        for rep in range(1 + max(1, args.steps)):
+            t0 = time.perf_counter()
+            N.check(N.lib().pl_filter_host(C.c_void_p(src.ctypes.data), C.c_void_p(feats.ctypes.data),
+                                           C.c_void_p(out.ctypes.data), n, 3, 5, C.c_void_p(0)))
+            t_our.append(time.perf_counter() - t0)
+        t_our = sorted(t_our[1:])[len(t_our[1:]) // 2]
+        # ours with device-resident buffers (what the CRF loop sees), lattice build included
+        fd, sd = torch.from_numpy(feats).to(dev), torch.from_numpy(src).to(dev)
+        od = torch.empty_like(sd)
+        for _ in range(2):
+            pkg.lattice.filter(sd, fd)
+        t_dev = _time(lambda: pkg.lattice.filter(sd, fd), 5, None, dev) * 1e-3
+        print(json.dumps({
+            "metric": "lattice_filter_mpix_labels_per_s", "unit": "Mpix*labels/s",
+            "config": {"workload": f"ref_cuda_filter_{h}x{w}_C3", "n": n, "channels": 3, "d": 5,
+                       "call": "host buffers in/out, lattice built inside the call"},
+            "reference_cuda": {"value": n * 3 / t_ref / 1e6, "ms": t_ref * 1e3,
+                               "source": "crf/lattice/cuda_lattice/permutohedral.cu rebuilt for sm_100a"},
+            "ours_host_call": {"value": n * 3 / t_our / 1e6, "ms": t_our * 1e3},
+            "ours_device_resident": {"value": n * 3 / t_dev / 1e6, "ms": t_dev * 1e3}}), flush=True)
+
+
 def crf_big(args, dev, rank, world, h, w, L, frames_total, name, sharded):
     import torch
     import torch.distributed as dist
@@ -193,7 +249,8 @@ def crf_big(args, dev, rank, world, h, w, L, frames_total, name, sharded):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", required=True,
-                    choices=["filter_sweep", "crf_full_L256", "crf_1080p_L128", "crf_tsukuba"])
+                    choices=["filter_sweep", "crf_full_L256", "crf_1080p_L128", "crf_tsukuba",
+                             "ref_cuda_filter"])
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--quick", action="store_true")
@@ -216,6 +273,9 @@ def main():
     if args.workload == "filter_sweep":
         if rank == 0:
             filter_sweep(args, dev)
+    elif args.workload == "ref_cuda_filter":
+        if rank == 0:
+            ref_cuda_filter(args, dev)
     elif args.workload == "crf_full_L256":
         crf_big(args, dev, rank, world, 1450, 2000, 256, 1, "middlebury_full_2000x1450_L256_5mf", True)
     elif args.workload == "crf_1080p_L128":

@@ -41,6 +41,31 @@ def build(force=False):
     return OUT
 
 
+CUDA_SRC = "/root/reference/crf/lattice/cuda_lattice/permutohedral.cu"
+OUT_CUDA = os.path.join(OUT_DIR, "libref_cuda_lattice.so")
+
+
+def build_cuda(force=False):
+    """The reference's stand-alone CUDA lattice (crf/lattice/cuda_lattice/permutohedral.cu, which
+    #includes hash_table.cu and the cutil.h vendored beside it) compiled IN PLACE for sm_100a in
+    LIBRARY mode: exports `filter(float* im, float* ref, int pd, int vd, int w, int h, bool
+    accurate)` (:523-529), host pointers in and out, vd <= 3.  A second SPEED baseline for the
+    filter sweep (bench_configs.py --workload ref_cuda_filter); its arithmetic is Adams'
+    normalised Gaussian, not the lite path's, so it is never used for parity."""
+    if not os.path.exists(CUDA_SRC):
+        return OUT_CUDA if os.path.exists(OUT_CUDA) else None
+    if not force and os.path.exists(OUT_CUDA) and os.path.getmtime(OUT_CUDA) >= os.path.getmtime(CUDA_SRC):
+        return OUT_CUDA
+    os.makedirs(OUT_DIR, exist_ok=True)
+    cmd = ["nvcc", "-w", "-O2", "-DLIBRARY", "-gencode", "arch=compute_100a,code=sm_100a", "-shared",
+           "-Xcompiler", "-fPIC", "-Xcompiler", "-w", "-I", os.path.dirname(CUDA_SRC),
+           "-include", os.path.join(HERE, "cuda_symbol_compat.h"), "-o", OUT_CUDA, CUDA_SRC, os.path.join(HERE, "cutil_shim.c")]
+    subprocess.check_call(cmd, cwd=OUT_DIR)
+    return OUT_CUDA
+
+
 if __name__ == "__main__":
     out = build(force="--force" in sys.argv)
     print(out if out else "reference sources absent and no prebuilt oracle/_ref")
+    out = build_cuda(force="--force" in sys.argv)
+    print(out if out else "reference CUDA sources absent and no prebuilt oracle/_ref")

@@ -109,7 +109,10 @@ def test_fused_depth_readout_matches_unfused(native, h, w, L, niters, labels):
     want = (q * lv[None]).sum(1)
     depth, label = lat.mean_field_depth(e0, mu, niters, 1.3, labels=lab, want_label=True)
     assert depth.shape == (h * w,) and label.dtype == torch.int32
-    assert _rel(depth.cpu(), want.cpu()) < 2e-5
+    # two runs of the loop differ by the order of the splat's atomic adds (~1e-7 per iteration,
+    # amplified by the soft-argmax at near-tie pixels): 3e-4 of the depth range across runs,
+    # 2e-5 for the read-out of one and the same E below
+    assert _rel(depth.cpu(), want.cpu()) < 3e-4
     assert (label.long() == e.argmin(1)).float().mean() > 0.999
     only_label = lat.mean_field_depth(e0, mu, niters, 1.3, want_depth=False, want_label=True)
     assert only_label[0] is None and torch.equal(only_label[1], label)
