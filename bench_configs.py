@@ -81,9 +81,9 @@ def filter_sweep(args, dev):
             if "lat" in box:
                 box["lat"].close()
             box["lat"] = pkg.PermutohedralLattice(feats)
-        for _ in range(2):
+        for _ in range(4):     # the stream-ordered pool grows during the first builds of a new size
             build()
-        t_build = _time(build, 3, flush, dev)
+        t_build = _time(build, 5, flush, dev)
         lat = box["lat"]
         M = lat.num_vertices
         for C in chans:
@@ -107,6 +107,57 @@ def filter_sweep(args, dev):
                              "scope": "whole filter apply (splat + blur + slice)"}}), flush=True)
             del src, out
         lat.close()
+
+
+def crf_train_step(args, dev):
+    """BASELINE config 2 as the reference trains it: CRFasRNN forward + backward through the
+    autograd operators (LatticeFilter.backward, gaussian_matrix.py:441-468), gradients wrt the
+    logits, gamma, s (compatibility) and s_ij, s_rgb (guide).  Also the cheaper step with the
+    guide frozen (no reference gradient: backward = one filter per iteration)."""
+    import time
+    import torch
+    import depth_estimation_b200 as pkg
+    cm = importlib.import_module("depth_estimation_b200.crf.crf_module")
+    gm = importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
+    synthetic = importlib.import_module("depth_estimation_b200.synthetic")
+    h, w, L, niters = (125, 185, 64, 5) if args.quick else (500, 740, 64, 5)
+    img = torch.from_numpy(synthetic.image(h, w, 0)).permute(2, 0, 1)[None].contiguous().to(dev)
+    logits0 = (-torch.from_numpy(synthetic.unary(h, w, L, 0))).reshape(h, w, L).permute(2, 0, 1)[None]
+    logits0 = logits0.contiguous().to(dev)
+    target = torch.from_numpy(synthetic.disparity(h, w, L, 0)).float()[None, None].to(dev)
+    labels = torch.arange(L, dtype=torch.float32, device=dev)
+    for name, train_guide in (("guide_trainable", True), ("guide_frozen", False)):
+        guide_mod = cm.ijrgbGuide(0.1, 0.1, trainable=train_guide).to(dev)
+        crf = cm.CRFasRNN(cm.charb(0.05), niters=niters).to(dev)
+
+        def step():
+            lg = logits0.clone().requires_grad_()
+            out = crf(guide_mod(img), lg)
+            depth = (torch.softmax(out, dim=1) * labels[None, :, None, None]).sum(1)[:, None]
+            loss = (depth - target).abs().mean()
+            loss.backward()
+            gm.clear_lattice_cache()
+            return loss
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize(dev)
+        ms = []
+        for _ in range(max(3, args.steps)):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            step()
+            b.record()
+            torch.cuda.synchronize(dev)
+            ms.append(a.elapsed_time(b))
+        ms.sort()
+        med = ms[len(ms) // 2]
+        peak_mem = torch.cuda.max_memory_allocated(dev) / 2 ** 30
+        print(json.dumps({"metric": "stereo_crf_train_steps_per_s", "unit": "steps/s", "value": 1e3 / med,
+                          "ms_per_step": med,
+                          "config": {"workload": f"crf_train_{h}x{w}_L{L}_{niters}mf_{name}", "h": h, "w": w,
+                                     "labels": L, "mf_iters": niters,
+                                     "grads": "logits, gamma, s" + (", s_ij, s_rgb" if train_guide else "")},
+                          "peak_mem_gib": peak_mem}), flush=True)
 
 
 def ref_cuda_filter(args, dev):
@@ -250,7 +301,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", required=True,
                     choices=["filter_sweep", "crf_full_L256", "crf_1080p_L128", "crf_tsukuba",
-                             "ref_cuda_filter"])
+                             "ref_cuda_filter", "crf_train_step", "build_profile"])
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--quick", action="store_true")
@@ -273,6 +324,26 @@ def main():
     if args.workload == "filter_sweep":
         if rank == 0:
             filter_sweep(args, dev)
+    elif args.workload == "crf_train_step":
+        if rank == 0:
+            crf_train_step(args, dev)
+    elif args.workload == "build_profile":
+        if rank == 0:
+            import depth_estimation_b200 as pkg
+            Nn = pkg._native
+            for (h, w) in [(2048, 2048), (4096, 2048)]:
+                feats = _features(h, w, 1, dev)
+                for _ in range(2):
+                    pkg.PermutohedralLattice(feats).close()
+                torch.cuda.synchronize(dev)
+                Nn.profile(True)
+                lat = pkg.PermutohedralLattice(feats)
+                torch.cuda.synchronize(dev)
+                Nn.profile(False)
+                rep = {k: round(v[1], 3) for k, v in Nn.profile_report().items()}
+                print(json.dumps({"workload": f"build_profile_{h}x{w}", "vertices": lat.num_vertices,
+                                  "kernel_ms": rep}), flush=True)
+                lat.close()
     elif args.workload == "ref_cuda_filter":
         if rank == 0:
             ref_cuda_filter(args, dev)

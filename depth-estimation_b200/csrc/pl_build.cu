@@ -28,6 +28,9 @@
 // The table capacity is >= 1.25 x entries so it can never fill; a bounded
 // probe count plus an overflow flag and a host retry guard the impossible.
 #include <math.h>
+#include <stdlib.h>
+
+#include <chrono>
 
 #include "pl_common.cuh"
 
@@ -473,8 +476,27 @@ uint64_t pow2_ceil(uint64_t x) {
   return p;
 }
 
+// PL_BUILD_TRACE=1: wall-clock per build phase on stderr (synchronises the stream at each point)
+struct BuildTrace {
+  bool on;
+  cudaStream_t st;
+  std::chrono::steady_clock::time_point t0;
+  explicit BuildTrace(cudaStream_t s) : on(getenv("PL_BUILD_TRACE") != nullptr), st(s) {
+    if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); }
+  }
+  void point(const char* what) {
+    if (!on) return;
+    cudaStreamSynchronize(st);
+    auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[pl build] %-28s %8.3f ms\n", what,
+            std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+
 template <int D>
 int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st) {
+  BuildTrace trace(st);
   constexpr int D1 = D + 1;
   const int64_t n = L->n;
   const uint64_t E = (uint64_t)n * D1;
@@ -488,12 +510,14 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
   PL_TRY(dev_alloc((void**)&L->vid, sizeof(int32_t) * E, st));
   L->bytes += (int64_t)((sizeof(int16_t) + sizeof(int8_t) + sizeof(float) + sizeof(int32_t)) * E);
 
+  trace.point("alloc point arrays");
   ScaleFactors sf;
   for (int i = 0; i < PL_MAX_D; i++) sf.s[i] = 0.f;
   reference_scale_factors(D, sf.s);
   PL_LAUNCH((elevate_kernel<D>), grid_for((uint64_t)n, 256, 8), 256, 0, st, ref, gs, n, sf, L->greedy,
             L->rank, L->bary);
 
+  trace.point("elevate");
   const uint32_t nchunks = ceil_div_u(E, kScanChunk);
   uint32_t* chunk_count = nullptr;  // [nchunks] + total + overflow flag
   PL_TRY(dev_alloc((void**)&chunk_count, sizeof(uint32_t) * ((size_t)nchunks + 2), st));
@@ -512,6 +536,7 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
     PL_TRY(dev_alloc((void**)&table, sizeof(unsigned long long) * cap, st));
     PL_CUDA(cudaMemsetAsync(table, 0xFF, sizeof(unsigned long long) * cap, st));
     PL_CUDA(cudaMemsetAsync(total_dev, 0, 2 * sizeof(uint32_t), st));
+    trace.point("alloc + clear hash table");
     PL_LAUNCH((insert_kernel<D>), grid_for((uint64_t)n, 256, 8), 256, 0, st, L->greedy, L->rank, n,
               table, (uint32_t)(cap - 1), L->vid, overflow_dev);
     PL_LAUNCH(count_first_kernel, nchunks, kScanThreads, 0, st, table, L->vid, E, chunk_count);
@@ -530,6 +555,7 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
   }
   const int64_t M = (int64_t)host_res[0];
   L->M = M;
+  trace.point("insert + count + scan + sync");
 
   int32_t* slot_vid = nullptr;
   PL_TRY(dev_alloc((void**)&slot_vid, sizeof(int32_t) * cap, st));
@@ -543,10 +569,13 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
   PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)M, 256, 8), 256, 0, st, table, slot_vid,
             L->vkeys, (uint32_t)(cap - 1), M, L->nbr);
 
+  trace.point("assign + gather + neighbours");
   dev_free(slot_vid, st);
   dev_free(table, st);
   dev_free(chunk_count, st);
-  return lattice_build_tiles(L, st);
+  const int rt = lattice_build_tiles(L, st);
+  trace.point("tile view");
+  return rt;
 }
 
 }  // namespace
