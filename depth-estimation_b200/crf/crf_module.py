@@ -96,6 +96,127 @@ class charb(nn.Module):
         return charbonneir(labels, x, self.gamma * labels.max()) * torch.exp(self.s)
 
 
+def _xty_accumulate(acc, a, b, chunk=4096):
+    """``acc += a^T b`` for tall ``a, b [n, L]``: a batched product over row chunks keeps every SM
+    busy (one [L, n] x [n, L] GEMM has L*L outputs and a 370 000-long reduction)."""
+    n, L = a.shape
+    k = n // chunk
+    if k > 1:
+        m = k * chunk
+        acc += torch.bmm(a[:m].view(k, chunk, L).transpose(1, 2), b[:m].view(k, chunk, L)).sum(0)
+        if m < n:
+            acc.addmm_(a[m:].t(), b[m:])
+    else:
+        acc.addmm_(a.t(), b)
+
+
+class _MeanFieldLoop(torch.autograd.Function):
+    """The loop of CRFasRNN.forward (crf_module.py:97-103) as ONE differentiable op, pixel-major.
+
+    forward : E_0 = E0;  Q_t = softmax(-E_t);  P_t = s * Q_t Mu^T;  E_{t+1} = E0 + K P_t - P_t
+              (``pl_softmax_compat`` on the tensor cores + the fused filter epilogue), keeping Q_t.
+    backward: exactly what autograd derives for the reference's composition -- the filter's
+              gradient wrt its source is the filter itself ("Matrix is symmetric",
+              gaussian_matrix.py:446), its gradient wrt the guide is gaussian_matrix.py:450-463 --
+              but without the NCHW <-> [n, L] round trips and the per-op temporaries:
+                  dP = K dE - dE;  dQ = s * dP Mu;  dMu += s * dP^T Q;  ds += <dP^T Q, Mu>
+                  dE_prev = -Q * (dQ - rowsum(dQ * Q));  dE0 += dE
+    Inputs / outputs are the module's NCHW tensors; returns E of the last iteration.
+    """
+
+    @staticmethod
+    def forward(ctx, E0, refs, mu, scale, niters):
+        from .gaussian_matrix import _grad_reference  # noqa: F401  (used in backward)
+        B, L, H, W = E0.shape
+        n, d = H * W, refs.shape[1]
+        dev = E0.device
+        E0c = E0.detach().float().contiguous()
+        e0 = torch.empty((B, n, L), dtype=torch.float32, device=dev)
+        st = N.stream_ptr(dev)
+        with torch.cuda.device(dev):
+            N.check(N.lib().pl_nchw_to_nlc(C.c_void_p(E0c.data_ptr()), C.c_void_p(e0.data_ptr()),
+                                           B, L, n, 1.0, st))
+        flat_refs = _cached(refs, lambda: refs.detach().reshape(B, d, -1).permute(0, 2, 1).contiguous())
+        if flat_refs.requires_grad:
+            flat_refs = flat_refs.detach()
+        mu_t = mu.detach().t().contiguous()
+        s = float(scale)
+        qs = []
+        e_out = torch.empty_like(e0)
+        for b in range(B):
+            lat = lattice_for(flat_refs[b])
+            e = e0[b]
+            per_iter = []
+            for _ in range(niters):
+                p = torch.empty((n, L), dtype=torch.float32, device=dev)
+                q = torch.empty((n, L), dtype=torch.float32, device=dev)
+                with torch.cuda.device(dev):
+                    N.check(N.lib().pl_softmax_compat(
+                        C.c_void_p(e.data_ptr()), C.c_void_p(mu_t.data_ptr()), C.c_void_p(p.data_ptr()),
+                        C.c_void_p(q.data_ptr()), n, L, s, st))
+                e = lat.filter(p, sub=p, add=e0[b])
+                per_iter.append(q)
+            e_out[b].copy_(e)
+            qs.append(per_iter)
+        ctx.qs, ctx.flat_refs, ctx.niters, ctx.shape = qs, flat_refs, niters, (B, L, H, W, d)
+        ctx.save_for_backward(mu.detach(), scale.detach() if torch.is_tensor(scale) else torch.tensor(s))
+        out = torch.empty((B, L, H, W), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            N.check(N.lib().pl_nlc_to_nchw(C.c_void_p(e_out.data_ptr()), C.c_void_p(out.data_ptr()),
+                                           B, L, n, 1.0, st))
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        from .gaussian_matrix import _grad_reference
+        mu, scale = ctx.saved_tensors
+        B, L, H, W, d = ctx.shape
+        n = H * W
+        dev = grad_out.device
+        s = float(scale)
+        need_e0, need_ref, need_mu, need_s = ctx.needs_input_grad[:4]
+        g = grad_out.float().contiguous()
+        dE_all = torch.empty((B, n, L), dtype=torch.float32, device=dev)
+        st = N.stream_ptr(dev)
+        with torch.cuda.device(dev):
+            N.check(N.lib().pl_nchw_to_nlc(C.c_void_p(g.data_ptr()), C.c_void_p(dE_all.data_ptr()),
+                                           B, L, n, 1.0, st))
+        dE0 = torch.zeros_like(dE_all)
+        dref = torch.zeros((B, n, d), dtype=torch.float32, device=dev) if need_ref else None
+        dM = torch.zeros((L, L), dtype=torch.float32, device=dev)     # sum_t dP_t^T Q_t (unscaled)
+        mu_c = mu.contiguous()
+        for b in range(B):
+            lat = lattice_for(ctx.flat_refs[b])
+            dE = dE_all[b]
+            for t in range(ctx.niters - 1, -1, -1):
+                q = ctx.qs[b][t]
+                dE0[b] += dE
+                if need_ref:
+                    p = torch.mm(q, mu_c.t()).mul_(s)                  # P_t, the filter's source
+                    gr, wg = _grad_reference(lat, p, ctx.flat_refs[b], dE)
+                    dref[b] += gr
+                    dP = wg.sub_(dE)
+                else:
+                    dP = lat.filter(dE, sub=dE)                        # K dE - dE
+                _xty_accumulate(dM, dP, q)
+                dQ = torch.mm(dP, mu_c).mul_(s)
+                # softmax(-E) backward: dE_prev = -Q * (dQ - sum_l dQ_l Q_l)
+                inner = (dQ * q).sum(1, keepdim=True)
+                dE = dQ.sub_(inner).mul_(q).neg_()
+            dE0[b] += dE
+        grad_E0 = grad_refs = None
+        if need_e0:
+            grad_E0 = torch.empty((B, L, H, W), dtype=torch.float32, device=dev)
+            with torch.cuda.device(dev):
+                N.check(N.lib().pl_nlc_to_nchw(C.c_void_p(dE0.data_ptr()), C.c_void_p(grad_E0.data_ptr()),
+                                               B, L, n, 1.0, st))
+        if need_ref:
+            grad_refs = dref.permute(0, 2, 1).reshape(B, d, H, W)
+        grad_mu = dM * s if need_mu else None
+        grad_s = (dM * mu_c).sum() if need_s else None
+        return grad_E0, grad_refs, grad_mu, grad_s, None
+
+
 class CRFasRNN(nn.Module):
     """crf_module.py:81-104 with the lattice pairwise term."""
 
@@ -122,6 +243,12 @@ class CRFasRNN(nn.Module):
             any(p.requires_grad for p in self.Mu.parameters()))
         if self.fused and not needs_grad and isinstance(self.Mu, charb) and self.niters > 0:
             return self._forward_fused(refs, E0, labels)
+        if self.fused and isinstance(self.Mu, charb) and self.niters > 0 and E0.is_cuda:
+            # training: the same loop as one autograd op (Mu and exp(s) stay torch expressions,
+            # so gamma, s, the labels and the guide's scales receive their gradients)
+            L = E0.shape[1]
+            mu = self.Mu.matrix(L, labels, E0.device).float()
+            return -_MeanFieldLoop.apply(E0, refs, mu, torch.exp(self.Mu.s), self.niters)
         Mu = (lambda q: self.Mu(q)) if labels is None else (lambda q: self.Mu(q, labels))
         Q = F.softmax(-E0, dim=1)
         for i in range(self.niters):
@@ -203,6 +330,27 @@ class CRFasRNN(nn.Module):
         return out
 
 
+_IJ_CACHE = {}
+
+
+def _ij_grid(bs, h, w, device):
+    """``np.tile(np.mgrid[:h, :w] / np.sqrt(h**2 + w**2), (bs, 1, 1, 1))`` as fp32 on ``device``
+    (crf_module.py:111-113).  Built on the device in float64 and cast, i.e. the same values the
+    reference computes on the host every call, without the host work and the pageable copy;
+    cached per (h, w, device)."""
+    key = (h, w, str(device))
+    ij = _IJ_CACHE.get(key)
+    if ij is None:
+        diag = float(np.sqrt(h ** 2 + w ** 2))
+        ii = (torch.arange(h, dtype=torch.float64, device=device) / diag)[:, None].expand(h, w)
+        jj = (torch.arange(w, dtype=torch.float64, device=device) / diag)[None, :].expand(h, w)
+        ij = torch.stack([ii, jj]).float().contiguous()
+        if len(_IJ_CACHE) > 8:
+            _IJ_CACHE.clear()
+        _IJ_CACHE[key] = ij
+    return ij[None].expand(bs, 2, h, w)
+
+
 class ijrgbGuide(nn.Module):
     """crf_module.py:106-114: guide = cat(ij / s_ij, rgb / s_rgb), ij = mgrid / sqrt(h^2+w^2)."""
 
@@ -213,8 +361,7 @@ class ijrgbGuide(nn.Module):
 
     def forward(self, x):
         bs, c, h, w = x.shape
-        ij = torch.from_numpy(np.tile(np.mgrid[:h, :w] / np.sqrt(h ** 2 + w ** 2),
-                                      (bs, 1, 1, 1))).float().to(x.device)
+        ij = _ij_grid(bs, h, w, x.device)
         return torch.cat([ij / self.s_ij, x / self.s_rgb], dim=1)
 
 
@@ -227,9 +374,7 @@ class ijGuide(nn.Module):
 
     def forward(self, x):
         bs, c, h, w = x.shape
-        ij = torch.from_numpy(np.tile(np.mgrid[:h, :w] / np.sqrt(h ** 2 + w ** 2),
-                                      (bs, 1, 1, 1))).float().to(x.device)
-        return ij / self.s_ij
+        return _ij_grid(bs, h, w, x.device) / self.s_ij
 
 
 def stereo_pair_depth(left, right, niters=5, gamma=.05, s=0., s_ij=.1, s_rgb=.1, window_size=9,
