@@ -234,10 +234,17 @@ def crf_big(args, dev, rank, world, h, w, L, frames_total, name, sharded):
     frames = 1 if sharded else max(1, frames_total // world)
     state = {}
 
+    peer = {}
+
     def step():
         for _ in range(frames):
             lat = pkg.PermutohedralLattice(feats)
-            if sharded and world > 1:
+            if sharded and world > 1 and args.peer:
+                if "b" not in peer:
+                    peer["b"] = ls.PeerMemoryBackend(lat, n, e0.shape[1])
+                peer["b"].lat = lat
+                out = peer["b"].run(e0, mu, 5, 1.0).clone()
+            elif sharded and world > 1:
                 out = ls.LabelShardedMeanField(ls.CudaBackend(lat)).run(e0, mu, 5, 1.0)
             else:
                 out = lat.mean_field(e0, mu, 5, 1.0)
@@ -287,7 +294,9 @@ def crf_big(args, dev, rank, world, h, w, L, frames_total, name, sharded):
             "scaling": "strong" if sharded else "weak", "dtype": "f32", "data": "synthetic",
             "config": {"workload": name, "h": h, "w": w, "labels": L, "mf_iters": 5, "d": D,
                        "frames_per_step": nframes, "vertices": M,
-                       "parallelism": (f"label-sharded x{world} (NCCL all-gather per iteration)"
+                       "parallelism": ((f"label-sharded x{world} (peer-memory reads inside the compat kernel)"
+                                        if args.peer else
+                                        f"label-sharded x{world} (NCCL all-gather per iteration)")
                                        if sharded and world > 1 else f"image-parallel x{world}"),
                        "l2": "inputs larger than L2"},
             "roofline": {"bound": "hbm", "achieved": per_frame * nframes / world / (ms * 1e-3) / 1e9,
@@ -307,6 +316,8 @@ def main():
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--profile", action="store_true", help="per-kernel CUDA-event times of one step")
     ap.add_argument("--frames", type=int, default=0)
+    ap.add_argument("--peer", action="store_true",
+                    help="label-sharded runs: read the peers' shards through CUDA IPC mappings")
     args = ap.parse_args()
     sys.stdout.flush()          # only JSON lines on stdout (NCCL's banner goes to stderr)
     real = os.dup(1)
@@ -356,6 +367,7 @@ def main():
         crf_big(args, dev, rank, world, 288, 384, 16, args.frames or 8 * world,
                 "tsukuba_384x288_L16_5mf", False)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

@@ -273,7 +273,8 @@ int pl_filter_host(const float* src_host, const float* ref_host, float* dst_host
 }
 
 static int compat_large(const float* e, int nblocks, const float* muT, float* p, float* q_out,
-                        int64_t n, int L, int l0, int N, float scale, cudaStream_t st);
+                        int64_t n, int L, int l0, int N, float scale, cudaStream_t st,
+                        const float* const* block_ptrs = nullptr);
 
 int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
                          int64_t n, int L, float scale, uint32_t flags, void* stream) {
@@ -299,11 +300,13 @@ int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev,
 }
 
 static int compat_large(const float* e, int nblocks, const float* muT, float* p, float* q_out,
-                        int64_t n, int L, int l0, int N, float scale, cudaStream_t st) {
+                        int64_t n, int L, int l0, int N, float scale, cudaStream_t st,
+                        const float* const* block_ptrs) {
   uint8_t* rec = nullptr;
   PL_TRY(pl::dev_alloc((void**)&rec, pl::compat_tc_mu_bytes(L, N), st));
   int r = pl::compat_tc_prepare_mu(muT, L, l0, N, rec, st);
-  if (r == PL_OK) r = pl::compat_tc_run(e, nblocks, L / nblocks, rec, p, q_out, n, L, N, scale, st);
+  if (r == PL_OK)
+    r = pl::compat_tc_run(e, nblocks, L / nblocks, rec, p, q_out, n, L, N, scale, st, block_ptrs);
   pl::dev_free(rec, st);
   return r;
 }
@@ -322,6 +325,66 @@ int pl_softmax_compat_blocked(const float* e_blocks_dev, int nblocks, const floa
   PL_TRY(pl::check_device());
   return compat_large(e_blocks_dev, nblocks, muT_dev, p_dev, nullptr, n, L, l0, N, scale,
                       (cudaStream_t)stream);
+}
+
+int pl_softmax_compat_peers(const float* const* e_block_ptrs, int nblocks, const float* muT_dev,
+                            float* p_dev, int64_t n, int L, int l0, int N, float scale,
+                            void* stream) {
+  if (e_block_ptrs == nullptr || muT_dev == nullptr || p_dev == nullptr || n <= 0 || nblocks < 1 ||
+      nblocks > 16 || L <= 0 || L % nblocks != 0 || l0 < 0 || N <= 0 || l0 + N > L ||
+      ((uintptr_t)p_dev & 15u) != 0 || !pl::compat_tc_supported(L, N, L / nblocks)) {
+    pl::set_last_error("pl_softmax_compat_peers: unsupported arguments (L=%d, N=%d, nblocks=%d)", L, N,
+                       nblocks);
+    return PL_ERR_INVALID;
+  }
+  for (int b = 0; b < nblocks; b++)
+    if (e_block_ptrs[b] == nullptr || ((uintptr_t)e_block_ptrs[b] & 15u) != 0) {
+      pl::set_last_error("pl_softmax_compat_peers: block %d is null or misaligned", b);
+      return PL_ERR_INVALID;
+    }
+  PL_TRY(pl::check_device());
+  return compat_large(e_block_ptrs[0], nblocks, muT_dev, p_dev, nullptr, n, L, l0, N, scale,
+                      (cudaStream_t)stream, e_block_ptrs);
+}
+
+// ---- peer memory (CUDA IPC) for the label shards ------------------------------------------
+int pl_peer_alloc(size_t bytes, void** dev_ptr_out, void* ipc_handle_out) {
+  if (dev_ptr_out == nullptr || ipc_handle_out == nullptr || bytes == 0) return PL_ERR_INVALID;
+  *dev_ptr_out = nullptr;
+  PL_TRY(pl::check_device());
+  PL_CUDA(cudaMalloc(dev_ptr_out, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, *dev_ptr_out);
+  if (e != cudaSuccess) {
+    cudaFree(*dev_ptr_out);
+    *dev_ptr_out = nullptr;
+    pl::set_last_error("cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+    return PL_ERR_CUDA;
+  }
+  static_assert(sizeof(cudaIpcMemHandle_t) == PL_IPC_HANDLE_BYTES, "handle size");
+  memcpy(ipc_handle_out, &h, sizeof(h));
+  return PL_OK;
+}
+
+int pl_peer_open(const void* ipc_handle, void** dev_ptr_out) {
+  if (ipc_handle == nullptr || dev_ptr_out == nullptr) return PL_ERR_INVALID;
+  *dev_ptr_out = nullptr;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, ipc_handle, sizeof(h));
+  PL_CUDA(cudaIpcOpenMemHandle(dev_ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+  return PL_OK;
+}
+
+int pl_peer_close(void* dev_ptr) {
+  if (dev_ptr == nullptr) return PL_OK;
+  PL_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+  return PL_OK;
+}
+
+int pl_peer_free(void* dev_ptr) {
+  if (dev_ptr == nullptr) return PL_OK;
+  PL_CUDA(cudaFree(dev_ptr));
+  return PL_OK;
 }
 
 int pl_softmax_compat(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,

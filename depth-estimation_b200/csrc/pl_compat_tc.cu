@@ -45,8 +45,15 @@ struct BCfg {
   static constexpr int REC = 2 * B_BYTES;            // hi | lo
 };
 
+constexpr int kMaxBlocks = 16;
+
 struct CArgs {
   const float* e;       // blocked [nblocks][n][block_w]
+  // Optional: block b lives at blk[b] ([n][block_w]) instead of e + b * n * block_w.  The
+  // pointers may be peer-GPU memory mapped through CUDA IPC (label shards read in place over
+  // NVLink, no all-gathered copy); blk[0] == e.
+  const float* blk[kMaxBlocks];
+  int use_blk;
   int nblocks, block_w;
   const uint8_t* mu_rec;  // [(L/64)][N/BN] records of BCfg<BN>::REC bytes
   float* p;             // [n][N]
@@ -102,7 +109,8 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
   for (int kc = 0; kc < kMaxKC; kc++) {
     const int label = kc * kKC + 4 * l;
     const int b = label / a.block_w;
-    eoff[kc] = (int64_t)b * a.n * a.block_w + (label - b * a.block_w);
+    eoff[kc] = (a.use_blk ? (int64_t)(a.blk[b < kMaxBlocks ? b : 0] - a.e)
+                          : (int64_t)b * a.n * a.block_w) + (label - b * a.block_w);
   }
   const int64_t bw = a.block_w;
 
@@ -366,8 +374,20 @@ int compat_tc_prepare_mu(const float* muT, int L, int l0, int N, uint8_t* mu_rec
 }
 
 int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_rec, float* p,
-                  float* q_out, int64_t n, int L, int N, float scale, cudaStream_t st) {
+                  float* q_out, int64_t n, int L, int N, float scale, cudaStream_t st,
+                  const float* const* block_ptrs) {
   CArgs a;
+  a.use_blk = 0;
+  for (int b = 0; b < kMaxBlocks; b++) a.blk[b] = nullptr;
+  if (block_ptrs != nullptr) {
+    if (nblocks > kMaxBlocks) {
+      set_last_error("at most %d label blocks", kMaxBlocks);
+      return PL_ERR_INVALID;
+    }
+    for (int b = 0; b < nblocks; b++) a.blk[b] = block_ptrs[b];
+    a.use_blk = 1;
+    e = block_ptrs[0];
+  }
   a.e = e; a.nblocks = nblocks; a.block_w = block_w; a.mu_rec = mu_rec; a.p = p; a.q_out = q_out;
   a.n = n; a.ntiles = (n + kSup * kTile - 1) / (kSup * kTile); a.L = L; a.N = N; a.scale = scale;
   a.debug = getenv("PL_CTC_DEBUG") ? atoi(getenv("PL_CTC_DEBUG")) : 0;

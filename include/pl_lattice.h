@@ -26,6 +26,7 @@
 #ifndef PL_LATTICE_H
 #define PL_LATTICE_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -146,6 +147,25 @@ int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev,
 int pl_softmax_compat_blocked(const float* e_blocks_dev, int nblocks, const float* muT_dev,
                               float* p_dev, int64_t n, int L, int l0, int N, float scale,
                               void* stream);
+
+/* pl_softmax_compat_blocked with the G label blocks at G separate addresses (host array of device
+ * pointers, each [n][L/G]).  The pointers may be PEER-GPU memory opened with pl_peer_open: every
+ * rank then reads the other ranks' E shards in place over NVLink inside the kernel that consumes
+ * them -- no all-gathered copy is written to or re-read from HBM.  The caller orders the ranks
+ * (the shards must be complete before the call: one tiny NCCL collective on the same stream). */
+int pl_softmax_compat_peers(const float* const* e_block_ptrs, int nblocks, const float* muT_dev,
+                            float* p_dev, int64_t n, int L, int l0, int N, float scale,
+                            void* stream);
+
+/* Device buffers other processes on this node can map (CUDA IPC; one process per GPU).
+ * pl_peer_alloc: cudaMalloc + export handle (PL_IPC_HANDLE_BYTES opaque bytes to send to the peers).
+ * pl_peer_open : map a peer's buffer into this process (not valid in the exporting process).
+ * pl_peer_close / pl_peer_free: unmap / free. */
+#define PL_IPC_HANDLE_BYTES 64
+int pl_peer_alloc(size_t bytes, void** dev_ptr_out, void* ipc_handle_out);
+int pl_peer_open(const void* ipc_handle, void** dev_ptr_out);
+int pl_peer_close(void* dev_ptr);
+int pl_peer_free(void* dev_ptr);
 
 /* Whole inference loop of CRFasRNN.forward (crf_module.py:93-104) with
  * W = lattice adjacency (gaussian_matrix.py:341-352), pixel-major:

@@ -88,3 +88,64 @@ def test_label_sharded_mean_field_matches_unsharded_and_oracle(native, oracle, h
         assert np.abs(got - e).max() / scale < 2e-4
         assert (got.argmin(1) == e.argmin(1)).mean() > 0.999
     assert native._native.lib().pl_debug_tc_timeouts() == 0
+
+
+@pytest.mark.parametrize("L,G", [(128, 2), (256, 4), (192, 3)])
+def test_compat_with_separate_block_pointers(native, L, G):
+    """pl_softmax_compat_peers: the G label blocks live in G separate allocations (what peer
+    mappings look like to the kernel) -- same result as the contiguous blocked layout."""
+    N = native._native
+    w, n = L // G, 515
+    g = torch.Generator().manual_seed(L + G)
+    e = torch.randn((n, L), generator=g) * 3
+    mu = torch.from_numpy(synthetic.charb_matrix(L)) + torch.rand((L, L), generator=g) * 0.1
+    want = (torch.softmax(-e.double(), dim=1) @ mu.double().t()) * 1.1
+    # separate tensors, deliberately allocated in reverse order with gaps in between
+    parts, pad = [None] * G, []
+    for b in reversed(range(G)):
+        pad.append(torch.empty(1000 + 37 * b, device="cuda"))
+        parts[b] = e[:, b * w:(b + 1) * w].contiguous().cuda()
+    mt = mu.t().contiguous().cuda()
+    ptrs = (C.c_void_p * G)(*[t.data_ptr() for t in parts])
+    for rank in range(G):
+        p = torch.full((n, w), float("nan"), device="cuda")
+        N.check(N.lib().pl_softmax_compat_peers(ptrs, G, C.c_void_p(mt.data_ptr()), C.c_void_p(p.data_ptr()),
+                                                n, L, rank * w, w, 1.1, N.stream_ptr(p.device)))
+        torch.cuda.synchronize()
+        assert _rel(p, want[:, rank * w:(rank + 1) * w]) < 1e-5, (L, G, rank)
+    assert N.lib().pl_debug_tc_timeouts() == 0
+
+
+def test_peer_memory_backend_single_process(native):
+    """world = 1: the IPC buffers, the torch views over them and the iteration order (the
+    multi-process form is tools/peer_check.py under torchrun, run by test_peer_shards_two_gpus)."""
+    ls = importlib.import_module("depth_estimation_b200.crf.label_shards")
+    h, w, L, niters = 40, 56, 128, 3
+    ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=1), 0.1, 0.1)
+    e0 = torch.from_numpy(synthetic.unary(h, w, L, seed=1)).cuda()
+    mu = torch.from_numpy(synthetic.charb_matrix(L) * 0.7).cuda()
+    lat = native.PermutohedralLattice(torch.from_numpy(ref).cuda())
+    want = lat.mean_field(e0, mu, niters, 1.1)
+    backend = ls.PeerMemoryBackend(lat, h * w, L)
+    try:
+        for _ in range(2):       # twice: the buffer parity carries over between runs
+            got = backend.run(e0, mu, niters, 1.1).clone()
+            assert _rel(got, want) < 2e-5
+    finally:
+        backend.close()
+
+
+def test_peer_shards_two_gpus(native):
+    """Two processes, two GPUs: peer-memory label sharding against the NCCL all-gather form and
+    the unsharded loop (skipped on a single-GPU box)."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29731", os.path.join(root, "tools", "peer_check.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "peer_check ok" in out.stdout
