@@ -14,11 +14,14 @@
 //     whole tile ahead: E0 / P_prev rows (one 4L-byte copy per row into a padded pitch, so
 //     the row-per-thread LDS.128 are bank-conflict free), the tile's distinct lattice rows,
 //     the packed slice / splat records.  No thread waits on a global load in steady state.
-//   * one CTA per SM (219 KB of shared memory); the MMA of tile k overlaps the slice of tile
+//   * the A operand never touches shared memory: the softmax threads write X hi / lo rows into
+//     TMEM with tcgen05.st (lane = pixel row, column = label) and the MMAs take A from there.
+//   * one CTA per SM (188 KB of shared memory); the MMA of tile k overlaps the slice of tile
 //     k+1, whose inputs are already resident.
 //   * normalisation by the row sum is deferred to the epilogue (P = acc * scale / sum), so
 //     the operand split does not wait for the sum exchange.
 #include <math.h>
+#include <stdlib.h>
 
 #include "pl_common.cuh"
 #include "pl_tc.cuh"
@@ -38,7 +41,7 @@ __device__ int g_row_timeouts = 0;
 
 constexpr int rmax(int a, int b) { return a > b ? a : b; }
 
-template <int L>
+template <int L, bool ATM = false>
 struct RCfg {
   static constexpr int CPT = L / 4;              // columns per thread
   static constexpr int KCH = L / 4;              // 16-byte K chunks per operand row
@@ -47,7 +50,8 @@ struct RCfg {
   static constexpr int A_BYTES = KCH * A_CH;
   static constexpr int B_BYTES = KCH * B_CH;
   static constexpr int PI = L + 4;               // padded row pitch in floats
-  static constexpr int Q_BYTES = rmax(2 * A_BYTES, kTile * PI * 4);
+  // A operand in TMEM (ATM): the region only stages the P tile
+  static constexpr int Q_BYTES = ATM ? kTile * PI * 4 : rmax(2 * A_BYTES, kTile * PI * 4);
   static constexpr int IN_BYTES = 2 * kTile * PI * 4;
   static constexpr int ROWS_BYTES = kStage * PI * 4;
   static constexpr int OFF_Q = 0;
@@ -59,7 +63,8 @@ struct RCfg {
   static constexpr int OFF_RED = OFF_RP + 9 * kTE;           // max[4][128] | sum[4][128]
   static constexpr int OFF_BAR = OFF_RED + 2 * 4 * kTile * 4;
   static constexpr int SMEM = OFF_BAR + 64 + 16;
-  static constexpr int TMEM_COLS = L < 32 ? 32 : L;
+  // ATM: D [0, L) | X hi [L, 2L) | X lo [2L, 3L), rounded up to a power of two
+  static constexpr int TMEM_COLS = ATM ? (L <= 32 ? 128 : 256) : (L < 32 ? 32 : L);
 };
 
 struct RowArgs {
@@ -103,9 +108,9 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
-template <int L, bool FIRST>
+template <int L, bool FIRST, bool ATM>
 __global__ void __launch_bounds__(kThreads, 1) mf_row_kernel(const RowArgs a) {
-  using C = RCfg<L>;
+  using C = RCfg<L, ATM>;
   constexpr int CPT = C::CPT, PI = C::PI;
   extern __shared__ __align__(128) unsigned char smem[];
   unsigned char* s_q = smem + C::OFF_Q;       // Q hi | lo planes -> P tile (pitch PI)
@@ -284,6 +289,7 @@ __global__ void __launch_bounds__(kThreads, 1) mf_row_kernel(const RowArgs a) {
       m = fmaxf(fmaxf(s_max[r], s_max[kTile + r]), fmaxf(s_max[2 * kTile + r], s_max[3 * kTile + r]));
       const float mb = -m * kLog2e;
       float sum = 0.f;
+      uint32_t xh[CPT], xl[CPT];   // ATM only (dead code otherwise)
 #pragma unroll
       for (int c4 = 0; c4 < CPT / 4; c4++) {
         float4 x, hi, lo;
@@ -296,13 +302,34 @@ __global__ void __launch_bounds__(kThreads, 1) mf_row_kernel(const RowArgs a) {
         hi.y = tc::tf32_rna(x.y); lo.y = tc::tf32_rna(x.y - hi.y);
         hi.z = tc::tf32_rna(x.z); lo.z = tc::tf32_rna(x.z - hi.z);
         hi.w = tc::tf32_rna(x.w); lo.w = tc::tf32_rna(x.w - hi.w);
-        const int ch = q * (CPT / 4) + c4;   // K chunk of the canonical A layout
-        *reinterpret_cast<float4*>(s_q + ch * C::A_CH + r * 16) = hi;
-        *reinterpret_cast<float4*>(s_q + C::A_BYTES + ch * C::A_CH + r * 16) = lo;
+        if (ATM) {
+          xh[4 * c4] = __float_as_uint(hi.x); xh[4 * c4 + 1] = __float_as_uint(hi.y);
+          xh[4 * c4 + 2] = __float_as_uint(hi.z); xh[4 * c4 + 3] = __float_as_uint(hi.w);
+          xl[4 * c4] = __float_as_uint(lo.x); xl[4 * c4 + 1] = __float_as_uint(lo.y);
+          xl[4 * c4 + 2] = __float_as_uint(lo.z); xl[4 * c4 + 3] = __float_as_uint(lo.w);
+        } else {
+          const int ch = q * (CPT / 4) + c4;   // K chunk of the canonical A layout
+          *reinterpret_cast<float4*>(s_q + ch * C::A_CH + r * 16) = hi;
+          *reinterpret_cast<float4*>(s_q + C::A_BYTES + ch * C::A_CH + r * 16) = lo;
+        }
+      }
+      if (ATM) {
+        // X hi / lo rows straight into TMEM (lane = row, column = label): the A operand of the
+        // MMAs, never staged in shared memory
+        const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+        if (CPT == 16) {
+          tc::tmem_st_x16(tmem + lane_base + (uint32_t)(L + col0), xh);
+          tc::tmem_st_x16(tmem + lane_base + (uint32_t)(2 * L + col0), xl);
+        } else {
+          tc::tmem_st_x8(tmem + lane_base + (uint32_t)(L + col0), xh);
+          tc::tmem_st_x8(tmem + lane_base + (uint32_t)(2 * L + col0), xl);
+        }
+        tc::tmem_st_wait();
       }
       s_sum[q * kTile + r] = sum;
     }
-    tc::fence_proxy_async();
+    if (ATM) tc::tcgen05_fence_before();
+    else tc::fence_proxy_async();
     __syncthreads();
 
     // ---- acc = X Mu^T on the tensor cores (3 x TF32 split): one thread issues ------------
@@ -318,9 +345,14 @@ __global__ void __launch_bounds__(kThreads, 1) mf_row_kernel(const RowArgs a) {
         const uint32_t bb = (pass == 1) ? b_lo : b_hi;
 #pragma unroll
         for (int ks = 0; ks < L / 8; ks++) {
-          const uint64_t ad = tc::smem_desc_kmajor(ab + ks * 2 * C::A_CH, C::A_CH, 128);
           const uint64_t bd = tc::smem_desc_kmajor(bb + ks * 2 * C::B_CH, C::B_CH, 128);
-          tc::mma_tf32_ss(tmem, ad, bd, idesc, (pass | ks) != 0);
+          if (ATM) {   // A: 8 TMEM columns of the hi (or lo) block
+            tc::mma_tf32_ts(tmem, tmem + (uint32_t)((pass == 0 ? 2 * L : L) + ks * 8), bd, idesc,
+                            (pass | ks) != 0);
+          } else {
+            const uint64_t ad = tc::smem_desc_kmajor(ab + ks * 2 * C::A_CH, C::A_CH, 128);
+            tc::mma_tf32_ss(tmem, ad, bd, idesc, (pass | ks) != 0);
+          }
         }
       }
       tc::mma_commit(&bars[1]);
@@ -426,18 +458,26 @@ __global__ void __launch_bounds__(kThreads, 1) mf_row_kernel(const RowArgs a) {
   if (warp == 0) tc::tmem_dealloc(tmem, C::TMEM_COLS);
 }
 
-template <int L, bool FIRST>
-int launch_row(const RowArgs& a, cudaStream_t st) {
-  using C = RCfg<L>;
+template <int L, bool FIRST, bool ATM>
+int launch_row_impl(const RowArgs& a, cudaStream_t st) {
+  using C = RCfg<L, ATM>;
   static bool attr_set = false;
   if (!attr_set) {
-    PL_CUDA(cudaFuncSetAttribute((mf_row_kernel<L, FIRST>),
+    PL_CUDA(cudaFuncSetAttribute((mf_row_kernel<L, FIRST, ATM>),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
     attr_set = true;
   }
   const unsigned grid = (unsigned)(a.ntiles < PL_SM_COUNT ? a.ntiles : PL_SM_COUNT);
-  PL_LAUNCH((mf_row_kernel<L, FIRST>), grid, kThreads, C::SMEM, st, a);
+  PL_LAUNCH((mf_row_kernel<L, FIRST, ATM>), grid, kThreads, C::SMEM, st, a);
   return PL_OK;
+}
+
+template <int L, bool FIRST>
+int launch_row(const RowArgs& a, cudaStream_t st) {
+  // The A operand (X hi / lo) goes registers -> TMEM (tcgen05.st) and the MMAs read it there;
+  // PL_MF_ROW_SMEM_A=1 (A/B knob) stages it in shared memory operand planes instead.
+  static const bool smem_a = getenv("PL_MF_ROW_SMEM_A") != nullptr;
+  return smem_a ? launch_row_impl<L, FIRST, false>(a, st) : launch_row_impl<L, FIRST, true>(a, st);
 }
 
 }  // namespace
