@@ -119,7 +119,7 @@ class _ClockSampler:
 def _algorithmic_bytes(kernel, n, M, C, launches_per_frame=None):
     """Per-launch algorithmic HBM bytes; d = 5, fp32."""
     d1 = D + 1
-    if kernel.startswith(("mf_row_kernel", "mf_tc_kernel", "mf_fused_kernel")):
+    if kernel.startswith(("mf_ws_kernel", "mf_row_kernel", "mf_tc_kernel", "mf_fused_kernel")):
         # fused iteration: first launch of a frame reads E0, writes P (+ splat record, lattice
         # rows written); the others also read P_prev, the slice record and the blurred lattice.
         first = 8 * n * C + 9 * n * d1 + 4 * M * C

@@ -443,7 +443,13 @@ static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT
       // the splat target: zeroed above (first iteration) or by the previous blur
       float* target = (res == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
       float* other = (target == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
-      if (use_row) {
+      // warp-specialised form (pl_fused_ws.cu) by default; PL_MEANFIELD_NO_WS=1 (A/B knob)
+      // falls back to the single-group row form (pl_fused_row.cu)
+      static const bool env_no_ws = getenv("PL_MEANFIELD_NO_WS") != nullptr;
+      if (use_row && !env_no_ws && pl::mf_ws_supported(Lt, L)) {
+        PL_TRY(pl::mf_ws_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
+                                   scale, L, st));
+      } else if (use_row) {
         PL_TRY(pl::mf_row_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
                                     scale, L, st));
       } else if (use_tc) {
@@ -584,7 +590,7 @@ int pl_profile_report(char* buf, int cap) {
 }
 
 uint64_t pl_launch_count(void) { return pl::g_launches; }
-int pl_debug_tc_timeouts(void) { return pl::tc_timeouts() + pl::ctc_timeouts() + pl::row_timeouts(); }
+int pl_debug_tc_timeouts(void) { return pl::tc_timeouts() + pl::ctc_timeouts() + pl::row_timeouts() + pl::ws_timeouts(); }
 int pl_version(void) { return PL_VERSION; }
 
 const char* pl_error_string(int code) {

@@ -135,6 +135,13 @@ int mf_row_iteration(Lattice* L, bool first, const float* val_in, float* val_out
                      const float* p_prev, float* p_next, const float* mu_canon, float scale,
                      int labels, cudaStream_t st);
 int row_timeouts();
+// the same iteration, warp-specialised: main group (slice / softmax / MMA / epilogue) and splat
+// group hand the P tile over through shared memory (pl_fused_ws.cu), L in {32, 64}, d = 5
+bool mf_ws_supported(const Lattice* L, int labels);
+int mf_ws_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
+                    const float* p_prev, float* p_next, const float* mu_canon, float scale,
+                    int labels, cudaStream_t st);
+int ws_timeouts();
 // softmax + compatibility for large label counts / label shards on tcgen05 (pl_compat_tc.cu)
 bool compat_tc_supported(int L, int N, int block_w);
 size_t compat_tc_mu_bytes(int L, int N);
