@@ -85,8 +85,8 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
   const int REC = rec_bytes(a.N), BCH = b_ch(a.N);
   unsigned char* s_a = smem;                              // A hi | lo planes; epilogue staging
   unsigned char* s_b = smem + kStageBytes;                // ring of Mu records
-  float* s_m = reinterpret_cast<float*>(s_b + a.ring * REC);   // [2][128] row max of -E
-  float* s_inv = s_m + 2 * kTile;                              // [2][128] 1 / row sum
+  float* s_m = reinterpret_cast<float*>(s_b + a.ring * REC);   // [2][128] row max of -E (this tile, next tile)
+  float* s_inv = s_m + 2 * kTile;                              // [128] 1 / row sum of this tile (+ 128 unused)
   int64_t* s_off = reinterpret_cast<int64_t*>(s_inv + 2 * kTile);   // [L/4] float4 group -> offset
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_off + kMaxL / 4);
   uint64_t* bar_full = bars;                  // [ring] Mu record landed
@@ -137,12 +137,31 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
     if (lane == 0) {
       const uint32_t total = my_tiles * (uint32_t)steps_per_tile;
       uint32_t rec = 0;
+      int64_t next_tile = (int64_t)blockIdx.x + gridDim.x;
       for (uint32_t t = 0; t < total; t++) {
         const uint32_t slot = t % a.ring, use = t / a.ring;
+        if (rec < (uint32_t)a.nblocks && !a.use_blk && next_tile < a.ntiles) {
+          // pull block `rec` of the NEXT tile's E rows into L2: its statistics pass (a whole tile
+          // later) then runs at L2 latency.  Local memory only: peer blocks bypass the local L2.
+          const int64_t q0 = next_tile * kTile;
+          const int64_t nrows = min((int64_t)kTile, a.n - q0);
+          const float* src = a.e + ((int64_t)rec * a.n + q0) * bw;
+          const uint32_t bytes = (uint32_t)(nrows * bw * 4);
+          for (uint32_t o = 0; o < bytes; o += 16384) {
+            const uint32_t sz = min(16384u, bytes - o);
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(
+                             reinterpret_cast<const char*>(src) + o),
+                         "r"(sz)
+                         : "memory");
+          }
+        }
         if (use > 0) wait_or_count(&bar_free[slot], (use - 1) & 1);
         tc::mbar_arrive_expect_tx(&bar_full[slot], REC);
         tc::tma_load_1d(s_b + slot * REC, a.mu_rec + (size_t)rec * REC, REC, &bar_full[slot]);
-        if (++rec == (uint32_t)steps_per_tile) rec = 0;
+        if (++rec == (uint32_t)steps_per_tile) {
+          rec = 0;
+          next_tile += gridDim.x;
+        }
       }
     }
   } else if (warp == 8) {
@@ -184,14 +203,12 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
     constexpr int RPT1 = kTile / (kSoft / 16);   // 8
     constexpr int RPT2 = kTile / (kSoft / 8);    // 4
 
-    // online softmax statistics of -E over all L labels for the tile at p0 -> s_m / s_inv [buf]
+    // row maximum of -E over all L labels for the tile at p0 -> s_m[buf].  The row sum is
+    // accumulated while the operands are staged and applied in the epilogue (one exp per value).
     auto statistics = [&](int64_t p0, int rows, int buf) {
-      float m[RPT1], sum[RPT1];
+      float m[RPT1];
 #pragma unroll
-      for (int i = 0; i < RPT1; i++) {
-        m[i] = -INFINITY;
-        sum[i] = 0.f;
-      }
+      for (int i = 0; i < RPT1; i++) m[i] = -INFINITY;
 #pragma unroll 2
       for (int s = 0; s < a.L / 64; s++) {
         const float* base = a.e + s_off[s * 16 + l] + p0 * bw;
@@ -203,30 +220,15 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
                             : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
-        for (int i = 0; i < RPT1; i++) {
-          const float mx = fmaxf(fmaxf(-e[i].x, -e[i].y), fmaxf(-e[i].z, -e[i].w));
-          const float mn = fmaxf(m[i], mx);
-          sum[i] = sum[i] * __expf(m[i] - mn) + __expf(-e[i].x - mn) + __expf(-e[i].y - mn) +
-                   __expf(-e[i].z - mn) + __expf(-e[i].w - mn);
-          m[i] = mn;
-        }
+        for (int i = 0; i < RPT1; i++)
+          m[i] = fmaxf(m[i], fmaxf(fmaxf(-e[i].x, -e[i].y), fmaxf(-e[i].z, -e[i].w)));
       }
 #pragma unroll
       for (int i = 0; i < RPT1; i++) {
-        const int r = g + i * 16;
-        float mi = m[i], si = sum[i];
+        float mi = m[i];
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) {  // combine the 16 lanes' (max, sum) pairs
-          const float m2 = __shfl_xor_sync(0xffffffffu, mi, o, 16);
-          const float s2 = __shfl_xor_sync(0xffffffffu, si, o, 16);
-          const float mn = fmaxf(mi, m2);
-          si = si * __expf(mi - mn) + s2 * __expf(m2 - mn);
-          mi = mn;
-        }
-        if (l == 0) {
-          s_m[buf * kTile + r] = mi;
-          s_inv[buf * kTile + r] = (r < rows) ? __fdividef(1.0f, si) : 0.f;
-        }
+        for (int o = 8; o > 0; o >>= 1) mi = fmaxf(mi, __shfl_xor_sync(0xffffffffu, mi, o, 16));
+        if (l == 0) s_m[buf * kTile + g + i * 16] = mi;
       }
     };
 
@@ -242,11 +244,11 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
       const int buf = t & 1;
 
       // ---- operand staging, K chunk by K chunk ----------------------------------------------
-      float rm[RPT2], rinv[RPT2];
+      float rm[RPT2], rsum[RPT2];
 #pragma unroll
       for (int i = 0; i < RPT2; i++) {
         rm[i] = s_m[buf * kTile + g2 + i * 32];
-        rinv[i] = s_inv[buf * kTile + g2 + i * 32];
+        rsum[i] = 0.f;
       }
       float4 ec[RPT2], en[RPT2];
       auto load_chunk = [&](int kc, float4* e) {
@@ -268,11 +270,12 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
           const int r = g2 + i * 32;
           float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
           if (r < rows) {
-            x.x = __expf(-ec[i].x - rm[i]) * rinv[i];
-            x.y = __expf(-ec[i].y - rm[i]) * rinv[i];
-            x.z = __expf(-ec[i].z - rm[i]) * rinv[i];
-            x.w = __expf(-ec[i].w - rm[i]) * rinv[i];
-            if (a.q_out != nullptr)
+            x.x = __expf(-ec[i].x - rm[i]);
+            x.y = __expf(-ec[i].y - rm[i]);
+            x.z = __expf(-ec[i].z - rm[i]);
+            x.w = __expf(-ec[i].w - rm[i]);
+            rsum[i] += (x.x + x.y) + (x.z + x.w);
+            if (a.q_out != nullptr)   // unnormalised here, scaled by 1 / sum after the tile
               *reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + kc * kKC + 4 * l2) = x;
           }
           float4 hi, lo;
@@ -291,6 +294,15 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
         for (int i = 0; i < RPT2; i++) ec[i] = en[i];
       }
 
+      // row sums: combine the 8 lanes of a row
+#pragma unroll
+      for (int i = 0; i < RPT2; i++) {
+        float si = rsum[i];
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) si += __shfl_xor_sync(0xffffffffu, si, o, 8);
+        if (l2 == 0) s_inv[g2 + i * 32] = (g2 + i * 32 < rows) ? __fdividef(1.0f, si) : 0.f;
+      }
+
       // ---- the next tile's statistics, while this tile's last MMAs drain ----------------------
       {
         const int64_t nt = tile + gridDim.x;
@@ -298,11 +310,26 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
       }
 
       // ---- epilogue: per 64-column block TMEM -> staging -> coalesced rows of P ----------------
+      bar_soft();   // row sums visible
+      if (a.q_out != nullptr) {   // Q = exp / sum: rescale the rows written during staging (L2-hot)
+        for (int i = 0; i < RPT1; i++) {
+          const int r = g + i * 16;
+          if (r >= rows) continue;
+          const float inv = s_inv[r];
+          for (int c = 4 * l; c < a.L; c += 64) {
+            float4* qp = reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + c);
+            float4 x = *qp;
+            x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
+            *qp = x;
+          }
+        }
+      }
       wait_or_count(bar_acc, t & 1);
       tc::tcgen05_fence_after();
       float* s_p = reinterpret_cast<float*>(s_a);
       const int q = warp & 3, hsel = warp >> 2;    // TMEM lane quarter; column half of the block
       const int row = q * 32 + lane;
+      const float rscale = a.scale * s_inv[row];
       for (int c0 = 0; c0 < a.N; c0 += 64) {
         const int cw = min(64, a.N - c0);          // 32 or 64
         const int cpw = cw >> 1;                   // columns per warp: 16 or 32
@@ -313,8 +340,8 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
 #pragma unroll
           for (int j = 0; j < 4; j++)
             *reinterpret_cast<float4*>(s_p + row * kPLD + col + 4 * j) =
-                make_float4(v[4 * j] * a.scale, v[4 * j + 1] * a.scale, v[4 * j + 2] * a.scale,
-                            v[4 * j + 3] * a.scale);
+                make_float4(v[4 * j] * rscale, v[4 * j + 1] * rscale, v[4 * j + 2] * rscale,
+                            v[4 * j + 3] * rscale);
         }
         if (c0 + 64 >= a.N) {      // last TMEM read of this tile: the accumulator may be overwritten
           tc::tcgen05_fence_before();
