@@ -85,6 +85,7 @@ static void lattice_release(Lattice* L, cudaStream_t st) {
   dev_free(L->rec_splat, st);
   dev_free(L->val[0], st);
   dev_free(L->val[1], st);
+  if (L->max_U_ev != nullptr) cudaEventDestroy(L->max_U_ev);
   delete L;
 }
 

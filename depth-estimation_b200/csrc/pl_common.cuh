@@ -85,6 +85,11 @@ struct Lattice {
   //   rec_splat[tile] = { ent_w f32[TE] | vertex id i32[TE] | ent_pix u8[TE] }  (sorted order)
   uint8_t* rec_slice = nullptr;
   uint8_t* rec_splat = nullptr;
+  // largest distinct-vertex count of a tile: reduced on the device after the tile build, copied
+  // to a pinned slot, read (after the event) by the first tiled slice to size its staging buffer
+  int max_U = -1;
+  int* h_max_U = nullptr;
+  cudaEvent_t max_U_ev = nullptr;
   // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats
   float* val[2] = {nullptr, nullptr};
   int64_t ws_floats = 0;     // floats per buffer

@@ -66,7 +66,7 @@ struct CArgs {
   int L, N;
   int ring;             // ring slots
   float scale;
-  int debug;  // timing experiments only: 1 = no MMAs
+  int debug;  // timing experiments only: 1 = no MMAs, 2 = no Mu copies, 4 = no statistics loads, 8 = no P stores
 };
 
 __host__ __device__ constexpr int b_ch(int N) { return N * 16 + 16; }       // one K chunk column of B
@@ -156,8 +156,12 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
           }
         }
         if (use > 0) wait_or_count(&bar_free[slot], (use - 1) & 1);
-        tc::mbar_arrive_expect_tx(&bar_full[slot], REC);
-        tc::tma_load_1d(s_b + slot * REC, a.mu_rec + (size_t)rec * REC, REC, &bar_full[slot]);
+        if (a.debug & 2) {
+          mbar_arrive(&bar_full[slot]);
+        } else {
+          tc::mbar_arrive_expect_tx(&bar_full[slot], REC);
+          tc::tma_load_1d(s_b + slot * REC, a.mu_rec + (size_t)rec * REC, REC, &bar_full[slot]);
+        }
         if (++rec == (uint32_t)steps_per_tile) {
           rec = 0;
           next_tile += gridDim.x;
@@ -210,7 +214,7 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
 #pragma unroll
       for (int i = 0; i < RPT1; i++) m[i] = -INFINITY;
 #pragma unroll 2
-      for (int s = 0; s < a.L / 64; s++) {
+      for (int s = 0; s < ((a.debug & 4) ? 0 : a.L / 64); s++) {
         const float* base = a.e + s_off[s * 16 + l] + p0 * bw;
         float4 e[RPT1];
 #pragma unroll
@@ -351,7 +355,7 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
 #pragma unroll
         for (int i = 0; i < RPT1; i++) {
           const int r = g + i * 16;
-          if (r < rows && 4 * l < cw)
+          if (r < rows && 4 * l < cw && !(a.debug & 8))
             *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
                 *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
         }

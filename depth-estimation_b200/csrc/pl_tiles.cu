@@ -368,6 +368,37 @@ int pow2_ceil_i(int x) {
 
 }  // namespace
 
+namespace {
+__global__ void max_u_kernel(const int* __restrict__ tile_U, int64_t ntiles, int* __restrict__ out);
+
+// pinned slots the devices report max U into (a ring: a stale slot can only cost speed, the
+// kernels decide staged / unstaged per tile from the tile's own U)
+int* pinned_slot() {
+  static int* ring = nullptr;
+  static unsigned next = 0;
+  constexpr unsigned kSlots = 4096;
+  if (ring == nullptr && cudaHostAlloc((void**)&ring, kSlots * sizeof(int), cudaHostAllocPortable) != cudaSuccess)
+    return nullptr;
+  return ring + (next++ % kSlots);
+}
+
+int tiles_max_u(Lattice* L, cudaStream_t st) {
+  int* d_max = L->tile_off + 2 * L->ntiles + 1;
+  PL_LAUNCH(max_u_kernel, grid_for((uint64_t)L->ntiles, 256, 1), 256, 0, st, L->tile_U, L->ntiles, d_max);
+  L->max_U = -1;
+  L->h_max_U = pinned_slot();
+  if (L->h_max_U == nullptr) {
+    (void)cudaGetLastError();
+    L->max_U = 1 << 30;   // unknown: largest staging buffer
+    return PL_OK;
+  }
+  PL_CUDA(cudaMemcpyAsync(L->h_max_U, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (L->max_U_ev == nullptr) PL_CUDA(cudaEventCreateWithFlags(&L->max_U_ev, cudaEventDisableTiming));
+  PL_CUDA(cudaEventRecord(L->max_U_ev, st));
+  return PL_OK;
+}
+}  // namespace
+
 int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   const int d1 = L->d + 1;
   const int TE = kTile * d1;
@@ -379,14 +410,14 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   PL_TRY(dev_alloc((void**)&L->ent_w, sizeof(float) * E_pad, st));
   PL_TRY(dev_alloc((void**)&L->loc, sizeof(uint16_t) * E_pad, st));
   PL_TRY(dev_alloc((void**)&L->useg, sizeof(int2) * E_pad, st));
-  PL_TRY(dev_alloc((void**)&L->tile_off, sizeof(int) * (size_t)(2 * ntiles + 1), st));
+  PL_TRY(dev_alloc((void**)&L->tile_off, sizeof(int) * (size_t)(2 * ntiles + 2), st));
   L->tile_U = L->tile_off + ntiles;
   int* counter = L->tile_off + 2 * ntiles;
   L->ntiles = ntiles;
   PL_TRY(dev_alloc((void**)&L->rec_slice, E_pad * 6, st));
   PL_TRY(dev_alloc((void**)&L->rec_splat, E_pad * 9, st));
   L->bytes += (int64_t)(E_pad * (1 + 4 + 2 + 8 + 6 + 9) + sizeof(int) * (size_t)(2 * ntiles + 1));
-  PL_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), st));
+  PL_CUDA(cudaMemsetAsync(counter, 0, 2 * sizeof(int), st));   // useg cursor, max U
   if (TE <= kFastMaxTE) {
     const size_t smem = sizeof(unsigned short) * (size_t)((TE + 31) / 32) * TE;
     // static (20.5 KB) + dynamic shared memory exceeds the 48 KB default: always opt in
@@ -395,7 +426,7 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
     PL_LAUNCH(tile_build_fast_kernel, (unsigned)ntiles, kThreads, smem, st, L->vid, L->bary, L->n,
               d1, L->ent_pix, L->ent_w, L->loc, L->useg, L->tile_off, L->tile_U, counter,
               L->rec_slice, L->rec_splat);
-    return PL_OK;
+    return tiles_max_u(L, st);
   }
   const size_t smem = sizeof(unsigned long long) * NS + sizeof(unsigned short) * (TE + 2);
   if (smem > 48 * 1024)
@@ -404,7 +435,7 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   PL_LAUNCH(tile_build_kernel, (unsigned)ntiles, kThreads, smem, st, L->vid, L->bary, L->n, d1, NS,
             L->ent_pix, L->ent_w, L->loc, L->useg, L->tile_off, L->tile_U, counter, L->rec_slice,
             L->rec_splat);
-  return PL_OK;
+  return tiles_max_u(L, st);
 }
 
 
@@ -413,7 +444,6 @@ namespace {
 constexpr int kCW = 64;             // channels per CTA pass (16 float4 lanes per row group)
 constexpr int kGroup = 16;          // lanes per row group
 constexpr int kGroups = kThreads / kGroup;
-constexpr int kStageRows = 160;     // vertex rows a slice CTA can stage (160 x 64 x 4 = 40 KB)
 
 __device__ __forceinline__ void red_add_v4(float* addr, float4 x) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(x.x), "f"(x.y),
@@ -421,142 +451,217 @@ __device__ __forceinline__ void red_add_v4(float* addr, float4 x) {
                : "memory");
 }
 
+// acc += w * x on both halves: one FFMA2 (the scalar weight is broadcast by the instruction)
+__device__ __forceinline__ void ffma2(float2& acc, float w, float2 x) {
+  unsigned long long a = *reinterpret_cast<unsigned long long*>(&acc);
+  float2 ww = make_float2(w, w);
+  asm("fma.rn.f32x2 %0, %1, %2, %0;"
+      : "+l"(a)
+      : "l"(*reinterpret_cast<unsigned long long*>(&ww)),
+        "l"(*reinterpret_cast<unsigned long long*>(&x)));
+  acc = *reinterpret_cast<float2*>(&a);
+}
+__device__ __forceinline__ void fma4(float4& acc, float w, const float4 x) {
+  float2 lo = make_float2(acc.x, acc.y), hi = make_float2(acc.z, acc.w);
+  ffma2(lo, w, make_float2(x.x, x.y));
+  ffma2(hi, w, make_float2(x.z, x.w));
+  acc = make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+
 // ---------------------------------------------------------------------------
 // splat, tiled.  grid = (tiles, channel blocks of kCW).   permutohedral.h:452-455
+//
+// The tile's (d+1) * 128 entries, sorted by vertex, are cut into 32 equal ranges; 8 lanes own a
+// range and 8 channels each (float4 indices l and l + 8 of the 64-channel block: every quarter
+// warp reads 128 contiguous bytes of one staged src row -> no bank conflicts).  A lane keeps the
+// running sum of the current vertex in registers and sends ONE red.global.add.v4 per float4 when
+// the vertex changes: balanced work whatever the segment lengths are, at most 31 extra flushes
+// per tile.  One 16-byte shared-memory record {weight, src row offset, vertex} per entry.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads)
+constexpr int kRanges = kThreads / 8;   // 32
+
+__global__ void __launch_bounds__(kThreads, 5)
 splat_tiled_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int64_t n, int d1,
-                   const uint8_t* __restrict__ ent_pix, const float* __restrict__ ent_w,
-                   const int2* __restrict__ useg, const int* __restrict__ tile_off,
-                   const int* __restrict__ tile_U, float* __restrict__ val) {
+                   const uint8_t* __restrict__ rec_splat, float* __restrict__ val) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* s_src = reinterpret_cast<float*>(smem_raw);                 // [kTile][kCW]
-  float* s_w = s_src + kTile * kCW;                                  // [TE]
-  uint8_t* s_pix = reinterpret_cast<uint8_t*>(s_w + kTile * d1);     // [TE]
+  float4* s_rec = reinterpret_cast<float4*>(s_src + kTile * kCW);    // [TE] {w, row offset, vertex, -}
 
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
   const int c0 = blockIdx.y * kCW;
   const int cw = min(kCW, Cc - c0);        // multiple of 4
-  const int V = cw >> 2;
   const int TE = kTile * d1;
   const int64_t p0 = tile * kTile;
   const int rows = (int)min((int64_t)kTile, n - p0);
 
-  // stage src rows (coalesced float4) and the tile's sorted entry list
-  for (int i = tid; i < rows * V; i += kThreads) {
-    const int r = i / V, v = i - r * V;
-    *reinterpret_cast<float4*>(s_src + r * kCW + 4 * v) =
-        *reinterpret_cast<const float4*>(src + (p0 + r) * src_stride + c0 + 4 * v);
+  // stage src rows (coalesced float4; rows past the end and channels past cw read as zero) ...
+  for (int i = tid; i < kTile * (kCW / 4); i += kThreads) {
+    const int r = i >> 4, v = i & 15;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < rows && 4 * v < cw)
+      x = *reinterpret_cast<const float4*>(src + (p0 + r) * src_stride + c0 + 4 * v);
+    *reinterpret_cast<float4*>(s_src + r * kCW + 4 * v) = x;
   }
-  const int valid = rows * d1;
-  for (int i = tid; i < valid; i += kThreads) {
-    s_w[i] = ent_w[tile * TE + i];
-    s_pix[i] = ent_pix[tile * TE + i];
-  }
+  // ... and the tile's sorted entry record (pads: weight 0 -> vertex 0, row 0)
+  const float* rp_w = reinterpret_cast<const float*>(rec_splat + tile * (int64_t)TE * 9);
+  const int32_t* rp_vid = reinterpret_cast<const int32_t*>(rp_w + TE);
+  const uint8_t* rp_pix = reinterpret_cast<const uint8_t*>(rp_vid + TE);
+  for (int i = tid; i < TE; i += kThreads)
+    s_rec[i] = make_float4(rp_w[i], __int_as_float((int)rp_pix[i] * kCW), __int_as_float(rp_vid[i]), 0.f);
   __syncthreads();
 
-  const int g = tid / kGroup, l = tid % kGroup;
-  const int U = tile_U[tile];
-  const int2* seg = useg + tile_off[tile];
-  if (l < V) {
-    for (int u = g; u < U; u += kGroups) {
-      const int2 sg = seg[u];
-      const int st = sg.y & 0xFFFF, cnt = sg.y >> 16;
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int k = st; k < st + cnt; k++) {
-        const float w = s_w[k];
-        const float4 x = *reinterpret_cast<const float4*>(s_src + (int)s_pix[k] * kCW + 4 * l);
-        // product rounded, then added: same two roundings as `val += w*value` (:455)
-        acc.x = __fadd_rn(acc.x, __fmul_rn(w, x.x));
-        acc.y = __fadd_rn(acc.y, __fmul_rn(w, x.y));
-        acc.z = __fadd_rn(acc.z, __fmul_rn(w, x.z));
-        acc.w = __fadd_rn(acc.w, __fmul_rn(w, x.w));
+  const int rg = tid >> 3, l = tid & 7;
+  const int ER = (TE + kRanges - 1) / kRanges;
+  const int k0 = rg * ER, k1 = min(TE, k0 + ER);
+  const bool on0 = 4 * l < cw, on1 = 32 + 4 * l < cw;
+  float* vbase = val + c0 + 4 * l;
+  int cur = -1;
+  float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+  for (int k = k0; k < k1; k++) {
+    const float4 rec = s_rec[k];
+    const int v = __float_as_int(rec.z);
+    if (v != cur) {
+      if (cur >= 0) {
+        if (on0) red_add_v4(vbase + (int64_t)cur * Cc, a0);
+        if (on1) red_add_v4(vbase + (int64_t)cur * Cc + 32, a1);
       }
-      red_add_v4(val + (int64_t)sg.x * Cc + c0 + 4 * l, acc);
+      cur = v;
+      a0 = make_float4(0.f, 0.f, 0.f, 0.f);
+      a1 = a0;
     }
+    const float* row = s_src + __float_as_int(rec.y) + 4 * l;
+    fma4(a0, rec.x, *reinterpret_cast<const float4*>(row));
+    fma4(a1, rec.x, *reinterpret_cast<const float4*>(row + 32));
+  }
+  if (cur >= 0) {
+    if (on0) red_add_v4(vbase + (int64_t)cur * Cc, a0);
+    if (on1) red_add_v4(vbase + (int64_t)cur * Cc + 32, a1);
   }
 }
 
 // ---------------------------------------------------------------------------
 // slice, tiled (+ fused epilogue).  grid = (tiles, channel blocks).  permutohedral.h:473-483
+//
+// 8 lanes per pixel row, 8 channels each (float4 indices l and l + 8), 4 rows per thread; the
+// epilogue operands (sub / add rows) are requested before the gather so their HBM latency hides
+// under it.  STAGE = vertex rows the CTA can stage, chosen per lattice from the largest tile.
 // ---------------------------------------------------------------------------
-template <bool EXACT>
-__global__ void __launch_bounds__(kThreads)
+template <bool EXACT, int STAGE>
+__global__ void __launch_bounds__(kThreads, 4)
 slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
-                   const uint16_t* __restrict__ loc, const float* __restrict__ bary,
-                   const int32_t* __restrict__ vid, const int2* __restrict__ useg,
-                   const int* __restrict__ tile_off, const int* __restrict__ tile_U, float denom,
-                   float* dst, int64_t dst_stride, const float* sub, int64_t sub_stride,
-                   const float* add, int64_t add_stride) {
+                   const uint8_t* __restrict__ rec_slice, const int32_t* __restrict__ vid,
+                   const int2* __restrict__ useg, const int* __restrict__ tile_off,
+                   const int* __restrict__ tile_U, float denom, float* dst, int64_t dst_stride,
+                   const float* sub, int64_t sub_stride, const float* add, int64_t add_stride) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  float* s_val = reinterpret_cast<float*>(smem_raw);                         // [kStageRows][kCW]
-  float* s_w = s_val + kStageRows * kCW;                                     // [TE]
-  int* s_idx = reinterpret_cast<int*>(s_w + kTile * d1);                     // [TE] local or global id
+  float* s_val = reinterpret_cast<float*>(smem_raw);                         // [STAGE][kCW]
+  float2* s_ent = reinterpret_cast<float2*>(s_val + STAGE * kCW);            // [TE] {weight, row}
 
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
   const int c0 = blockIdx.y * kCW;
   const int cw = min(kCW, Cc - c0);
-  const int V = cw >> 2;
   const int TE = kTile * d1;
   const int64_t p0 = tile * kTile;
   const int rows = (int)min((int64_t)kTile, n - p0);
   const int U = tile_U[tile];
-  const bool staged = U <= kStageRows;   // uniform per CTA
+  const bool staged = U <= STAGE;   // uniform per CTA
   const float inv = 1.0f / denom;
 
   if (staged) {
     const int2* seg = useg + tile_off[tile];
-    for (int i = tid; i < U * V; i += kThreads) {
-      const int u = i / V, v = i - u * V;
-      *reinterpret_cast<float4*>(s_val + u * kCW + 4 * v) =
-          *reinterpret_cast<const float4*>(val + (int64_t)seg[u].x * Cc + c0 + 4 * v);
+    for (int i = tid; i < U * 16; i += kThreads) {
+      const int u = i >> 4, v = i & 15;
+      if (4 * v < cw)
+        *reinterpret_cast<float4*>(s_val + u * kCW + 4 * v) =
+            *reinterpret_cast<const float4*>(val + (int64_t)seg[u].x * Cc + c0 + 4 * v);
     }
   }
+  const float* rs_bary = reinterpret_cast<const float*>(rec_slice + tile * (int64_t)TE * 6);
+  const uint16_t* rs_loc = reinterpret_cast<const uint16_t*>(rs_bary + TE);
   const int valid = rows * d1;
-  for (int i = tid; i < valid; i += kThreads) {
-    s_w[i] = bary[tile * TE + i];
-    s_idx[i] = staged ? (int)loc[tile * TE + i] : vid[tile * TE + i];
+  for (int i = tid; i < TE; i += kThreads) {
+    int ix = 0;
+    if (i < valid) ix = staged ? (int)rs_loc[i] * kCW : vid[tile * TE + i];
+    s_ent[i] = make_float2(rs_bary[i], __int_as_float(ix));
   }
   __syncthreads();
 
-  const int g = tid / kGroup, l = tid % kGroup;
-  if (l >= V) return;
-  for (int r = g; r < rows; r += kGroups) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int j = 0; j < d1; j++) {
-      const float w = s_w[r * d1 + j];
-      const int ix = s_idx[r * d1 + j];
-      const float4 x = staged
-                           ? *reinterpret_cast<const float4*>(s_val + ix * kCW + 4 * l)
-                           : *reinterpret_cast<const float4*>(val + (int64_t)ix * Cc + c0 + 4 * l);
-      if (EXACT) {
-        acc.x = __fadd_rn(acc.x, __fdiv_rn(__fmul_rn(w, x.x), denom));
-        acc.y = __fadd_rn(acc.y, __fdiv_rn(__fmul_rn(w, x.y), denom));
-        acc.z = __fadd_rn(acc.z, __fdiv_rn(__fmul_rn(w, x.z), denom));
-        acc.w = __fadd_rn(acc.w, __fdiv_rn(__fmul_rn(w, x.w), denom));
-      } else {
-        const float wi = w * inv;
-        acc.x = __fmaf_rn(wi, x.x, acc.x);
-        acc.y = __fmaf_rn(wi, x.y, acc.y);
-        acc.z = __fmaf_rn(wi, x.z, acc.z);
-        acc.w = __fmaf_rn(wi, x.w, acc.w);
-      }
-    }
+  const int g = tid >> 3, l = tid & 7;
+  const bool on0 = 4 * l < cw, on1 = 32 + 4 * l < cw;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+  for (int r = g; r < rows; r += kThreads / 8) {
     const int64_t p = p0 + r;
+    float4 s0 = zero, s1 = zero, t0 = zero, t1 = zero;
     if (sub != nullptr) {
-      const float4 s = *reinterpret_cast<const float4*>(sub + p * sub_stride + c0 + 4 * l);
-      acc.x = __fsub_rn(acc.x, s.x); acc.y = __fsub_rn(acc.y, s.y);
-      acc.z = __fsub_rn(acc.z, s.z); acc.w = __fsub_rn(acc.w, s.w);
+      const float* q = sub + p * sub_stride + c0 + 4 * l;
+      if (on0) s0 = *reinterpret_cast<const float4*>(q);
+      if (on1) s1 = *reinterpret_cast<const float4*>(q + 32);
     }
     if (add != nullptr) {
-      const float4 s = *reinterpret_cast<const float4*>(add + p * add_stride + c0 + 4 * l);
-      acc.x = __fadd_rn(s.x, acc.x); acc.y = __fadd_rn(s.y, acc.y);
-      acc.z = __fadd_rn(s.z, acc.z); acc.w = __fadd_rn(s.w, acc.w);
+      const float* q = add + p * add_stride + c0 + 4 * l;
+      if (on0) t0 = *reinterpret_cast<const float4*>(q);
+      if (on1) t1 = *reinterpret_cast<const float4*>(q + 32);
     }
-    *reinterpret_cast<float4*>(dst + p * dst_stride + c0 + 4 * l) = acc;
+    float4 a0 = zero, a1 = zero;
+    for (int j = 0; j < d1; j++) {
+      const float2 e = s_ent[r * d1 + j];
+      const int ix = __float_as_int(e.y);
+      float4 x0, x1;
+      if (staged) {
+        x0 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l);
+        x1 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l + 32);
+      } else {
+        const float* q = val + (int64_t)ix * Cc + c0 + 4 * l;
+        x0 = on0 ? *reinterpret_cast<const float4*>(q) : zero;
+        x1 = on1 ? *reinterpret_cast<const float4*>(q + 32) : zero;
+      }
+      if (EXACT) {
+        const float w = e.x;
+        a0.x = __fadd_rn(a0.x, __fdiv_rn(__fmul_rn(w, x0.x), denom));
+        a0.y = __fadd_rn(a0.y, __fdiv_rn(__fmul_rn(w, x0.y), denom));
+        a0.z = __fadd_rn(a0.z, __fdiv_rn(__fmul_rn(w, x0.z), denom));
+        a0.w = __fadd_rn(a0.w, __fdiv_rn(__fmul_rn(w, x0.w), denom));
+        a1.x = __fadd_rn(a1.x, __fdiv_rn(__fmul_rn(w, x1.x), denom));
+        a1.y = __fadd_rn(a1.y, __fdiv_rn(__fmul_rn(w, x1.y), denom));
+        a1.z = __fadd_rn(a1.z, __fdiv_rn(__fmul_rn(w, x1.z), denom));
+        a1.w = __fadd_rn(a1.w, __fdiv_rn(__fmul_rn(w, x1.w), denom));
+      } else {
+        const float wi = e.x * inv;
+        fma4(a0, wi, x0);
+        fma4(a1, wi, x1);
+      }
+    }
+    if (sub != nullptr) {
+      a0.x = __fsub_rn(a0.x, s0.x); a0.y = __fsub_rn(a0.y, s0.y);
+      a0.z = __fsub_rn(a0.z, s0.z); a0.w = __fsub_rn(a0.w, s0.w);
+      a1.x = __fsub_rn(a1.x, s1.x); a1.y = __fsub_rn(a1.y, s1.y);
+      a1.z = __fsub_rn(a1.z, s1.z); a1.w = __fsub_rn(a1.w, s1.w);
+    }
+    if (add != nullptr) {
+      a0.x = __fadd_rn(t0.x, a0.x); a0.y = __fadd_rn(t0.y, a0.y);
+      a0.z = __fadd_rn(t0.z, a0.z); a0.w = __fadd_rn(t0.w, a0.w);
+      a1.x = __fadd_rn(t1.x, a1.x); a1.y = __fadd_rn(t1.y, a1.y);
+      a1.z = __fadd_rn(t1.z, a1.z); a1.w = __fadd_rn(t1.w, a1.w);
+    }
+    float* q = dst + p * dst_stride + c0 + 4 * l;
+    if (on0) *reinterpret_cast<float4*>(q) = a0;
+    if (on1) *reinterpret_cast<float4*>(q + 32) = a1;
   }
+}
+
+// largest distinct-vertex count over the tiles (sizes the slice kernel's staging buffer)
+__global__ void __launch_bounds__(256) max_u_kernel(const int* __restrict__ tile_U, int64_t ntiles,
+                                                    int* __restrict__ out) {
+  int m = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ntiles;
+       i += (int64_t)gridDim.x * blockDim.x)
+    m = max(m, tile_U[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
 }
 
 }  // namespace
@@ -565,43 +670,58 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
                 cudaStream_t st) {
   const int d1 = L->d + 1;
-  const size_t smem = sizeof(float) * kTile * kCW + (sizeof(float) + 1) * (size_t)kTile * d1 + 16;
+  const size_t smem = sizeof(float) * kTile * kCW + sizeof(float4) * (size_t)kTile * d1;
   static bool attr_done = false;
-  if (!attr_done && smem > 48 * 1024) {
+  if (!attr_done) {
     PL_CUDA(cudaFuncSetAttribute(splat_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smem));
+                                 100 * 1024));
     attr_done = true;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
   PL_LAUNCH(splat_tiled_kernel, grid, kThreads, smem, st, src, src_stride, Cc, L->n, d1,
-            L->ent_pix, L->ent_w, L->useg, L->tile_off, L->tile_U, val);
+            L->rec_splat, val);
   return PL_OK;
 }
 
-int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, int64_t dst_stride,
-                const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
-                bool exact, cudaStream_t st) {
+namespace {
+template <bool EXACT, int STAGE>
+int launch_slice(Lattice* L, const float* val, int Cc, float denom, float* dst, int64_t dst_stride,
+                 const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
+                 cudaStream_t st) {
   const int d1 = L->d + 1;
-  const size_t smem = sizeof(float) * kStageRows * kCW + 2 * sizeof(float) * (size_t)kTile * d1;
+  const size_t smem = sizeof(float) * STAGE * kCW + sizeof(float2) * (size_t)kTile * d1;
   static bool attr_done = false;
   if (!attr_done) {
-    PL_CUDA(cudaFuncSetAttribute(slice_tiled_kernel<false>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    PL_CUDA(cudaFuncSetAttribute(slice_tiled_kernel<true>,
+    PL_CUDA(cudaFuncSetAttribute((slice_tiled_kernel<EXACT, STAGE>),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_done = true;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
-  if (exact) {
-    PL_LAUNCH((slice_tiled_kernel<true>), grid, kThreads, smem, st, val, Cc, L->n, d1, L->loc,
-              L->bary, L->vid, L->useg, L->tile_off, L->tile_U, denom, dst, dst_stride, sub,
-              sub_stride, add, add_stride);
-  } else {
-    PL_LAUNCH((slice_tiled_kernel<false>), grid, kThreads, smem, st, val, Cc, L->n, d1, L->loc,
-              L->bary, L->vid, L->useg, L->tile_off, L->tile_U, denom, dst, dst_stride, sub,
-              sub_stride, add, add_stride);
-  }
+  PL_LAUNCH((slice_tiled_kernel<EXACT, STAGE>), grid, kThreads, smem, st, val, Cc, L->n, d1,
+            L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, dst, dst_stride, sub,
+            sub_stride, add, add_stride);
   return PL_OK;
+}
+}  // namespace
+
+int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, int64_t dst_stride,
+                const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
+                bool exact, cudaStream_t st) {
+  if (L->max_U < 0) {   // first tiled slice on this lattice: the tile build has long finished
+    PL_CUDA(cudaEventSynchronize(L->max_U_ev));
+    L->max_U = *L->h_max_U;
+  }
+#define PL_SLICE(EX, ST) \
+  return launch_slice<EX, ST>(L, val, Cc, denom, dst, dst_stride, sub, sub_stride, add, add_stride, st)
+  if (exact) {
+    if (L->max_U <= 48) PL_SLICE(true, 48);
+    if (L->max_U <= 96) PL_SLICE(true, 96);
+    PL_SLICE(true, 160);
+  }
+  if (L->max_U <= 48) PL_SLICE(false, 48);
+  if (L->max_U <= 96) PL_SLICE(false, 96);
+  PL_SLICE(false, 160);
+#undef PL_SLICE
 }
 
 }  // namespace pl
