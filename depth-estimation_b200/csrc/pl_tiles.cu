@@ -17,6 +17,7 @@
 // Feature sets without locality (U close to kTile*(d+1)) simply fall back to
 // per-entry global access inside the same kernels.
 #include <math.h>
+#include <stdlib.h>
 
 #include "pl_common.cuh"
 
@@ -443,7 +444,6 @@ namespace {
 
 constexpr int kCW = 64;             // channels per CTA pass (16 float4 lanes per row group)
 constexpr int kGroup = 16;          // lanes per row group
-constexpr int kGroups = kThreads / kGroup;
 
 __device__ __forceinline__ void red_add_v4(float* addr, float4 x) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(x.x), "f"(x.y),
@@ -535,6 +535,124 @@ splat_tiled_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, in
     fma4(a1, rec.x, *reinterpret_cast<const float4*>(row + 32));
   }
   if (cur >= 0) {
+    if (on0) red_add_v4(vbase + (int64_t)cur * Cc, a0);
+    if (on1) red_add_v4(vbase + (int64_t)cur * Cc + 32, a1);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// splat, tiled, d = 5: the same ranges, software-pipelined.  Persistent CTAs (two per SM) walk a
+// contiguous run of (tile, channel block) items; while item i is summed, cp.async brings the src
+// rows and the raw entry record of item i+1 into the other buffers, so no warp waits on HBM in
+// steady state.  A lane keeps 3 of its range's 24 entries {weight, vertex << 7 | row} in registers
+// and the 8 lanes of the range hand them round with shuffles: per entry two 128-byte shared-memory
+// reads (the src row) and nothing else.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src, bool valid) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  const int sz = valid ? 16 : 0;   // 0: zero-fill, nothing is read
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+constexpr int kD1p = 6;                       // d + 1 of the pipelined kernel
+constexpr int kTEp = kTile * kD1p;            // 768 entries
+constexpr int kERp = kTEp / kRanges;          // 24 entries per range
+constexpr int kRecRaw = kTEp * 9;             // bytes of a raw splat record
+
+__global__ void __launch_bounds__(kThreads, 2)
+splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int64_t n, int nblk,
+                  int64_t nitems, const uint8_t* __restrict__ rec_splat, float* __restrict__ val) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* s_src = reinterpret_cast<float*>(smem_raw);                    // [2][kTile][kCW]
+  unsigned char* s_raw = smem_raw + 2 * kTile * kCW * sizeof(float);    // [2][kRecRaw]
+
+  const int tid = threadIdx.x;
+  const int64_t per = (nitems + gridDim.x - 1) / gridDim.x;
+  const int64_t i0 = blockIdx.x * per, i1 = min(nitems, i0 + per);
+  if (i0 >= i1) return;
+
+  auto request = [&](int64_t item, int sbuf, int rbuf, bool with_rec) {
+    const int64_t tile = item / nblk;
+    const int c0 = (int)(item - tile * nblk) * kCW;
+    const int cw = min(kCW, Cc - c0);
+    const int64_t p0 = tile * kTile;
+    const int rows = (int)min((int64_t)kTile, n - p0);
+    float* dst = s_src + sbuf * (kTile * kCW);
+#pragma unroll
+    for (int k = 0; k < kTile * (kCW / 4) / kThreads; k++) {
+      const int i = tid + k * kThreads;
+      const int r = i >> 4, v = i & 15;
+      const bool ok = r < rows && 4 * v < cw;
+      cp_async16(dst + r * kCW + 4 * v, ok ? src + (p0 + r) * src_stride + c0 + 4 * v : src, ok);
+    }
+    if (with_rec) {
+      const unsigned char* g = rec_splat + tile * (int64_t)kRecRaw;
+      for (int i = tid; i < kRecRaw / 16; i += kThreads)
+        cp_async16(s_raw + rbuf * kRecRaw + i * 16, g + i * 16, true);
+    }
+    cp_async_commit();
+  };
+
+  const int rg = tid >> 3, l = tid & 7;
+  int rbuf = 0;
+  int64_t cur_tile = i0 / nblk;
+  request(i0, 0, 0, true);
+  for (int64_t item = i0; item < i1; item++) {
+    const int sbuf = (int)(item - i0) & 1;
+    cp_async_wait_all();
+    __syncthreads();   // item's buffers landed; everyone is done with the other buffers
+    const int64_t tile = item / nblk;
+    if (tile != cur_tile) {
+      cur_tile = tile;
+      rbuf ^= 1;
+    }
+    if (item + 1 < i1) {
+      const bool new_tile = (item + 1) / nblk != tile;
+      request(item + 1, sbuf ^ 1, rbuf ^ 1, new_tile);
+    }
+    const int c0 = (int)(item - tile * nblk) * kCW;
+    const int cw = min(kCW, Cc - c0);
+    const bool on0 = 4 * l < cw, on1 = 32 + 4 * l < cw;
+
+    // this lane's 3 entries of the range
+    const float* rw = reinterpret_cast<const float*>(s_raw + rbuf * kRecRaw);
+    const int* rv = reinterpret_cast<const int*>(rw + kTEp);
+    const uint8_t* rp = reinterpret_cast<const uint8_t*>(rv + kTEp);
+    float w[3];
+    int key[3];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const int k = rg * kERp + j * 8 + l;
+      w[j] = rw[k];
+      key[j] = (rv[k] << 7) | (int)rp[k];
+    }
+    const float* sb = s_src + sbuf * (kTile * kCW) + 4 * l;
+    float* vbase = val + c0 + 4 * l;
+    int cur = -1;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const float wk = __shfl_sync(0xffffffffu, w[j], i, 8);
+        const int kk = __shfl_sync(0xffffffffu, key[j], i, 8);
+        const int v = kk >> 7;
+        if (v != cur) {
+          if (cur >= 0) {
+            if (on0) red_add_v4(vbase + (int64_t)cur * Cc, a0);
+            if (on1) red_add_v4(vbase + (int64_t)cur * Cc + 32, a1);
+          }
+          cur = v;
+          a0 = make_float4(0.f, 0.f, 0.f, 0.f);
+          a1 = a0;
+        }
+        const float* row = sb + (kk & 127) * kCW;
+        fma4(a0, wk, *reinterpret_cast<const float4*>(row));
+        fma4(a1, wk, *reinterpret_cast<const float4*>(row + 32));
+      }
+    }
     if (on0) red_add_v4(vbase + (int64_t)cur * Cc, a0);
     if (on1) red_add_v4(vbase + (int64_t)cur * Cc + 32, a1);
   }
@@ -675,7 +793,19 @@ int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float*
   if (!attr_done) {
     PL_CUDA(cudaFuncSetAttribute(splat_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  100 * 1024));
+    PL_CUDA(cudaFuncSetAttribute(splat_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 100 * 1024));
     attr_done = true;
+  }
+  static const bool no_pipe = getenv("PL_SPLAT_NO_PIPE") != nullptr;
+  if (d1 == kD1p && !no_pipe && L->M < (1 << 24)) {   // vertex id and row share one 32-bit key
+    const int nblk = (Cc + kCW - 1) / kCW;
+    const int64_t nitems = L->ntiles * nblk;
+    const size_t smem_p = 2 * sizeof(float) * kTile * kCW + 2 * (size_t)kRecRaw;
+    const int64_t cap = 2 * PL_SM_COUNT;
+    PL_LAUNCH(splat_pipe_kernel, (unsigned)(nitems < cap ? nitems : cap), kThreads, smem_p, st, src,
+              src_stride, Cc, L->n, nblk, nitems, L->rec_splat, val);
+    return PL_OK;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
   PL_LAUNCH(splat_tiled_kernel, grid, kThreads, smem, st, src, src_stride, Cc, L->n, d1,
