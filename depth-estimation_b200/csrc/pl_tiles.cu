@@ -665,8 +665,8 @@ splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int
 // epilogue operands (sub / add rows) are requested before the gather so their HBM latency hides
 // under it.  STAGE = vertex rows the CTA can stage, chosen per lattice from the largest tile.
 // ---------------------------------------------------------------------------
-template <bool EXACT, int STAGE>
-__global__ void __launch_bounds__(kThreads, 4)
+template <bool EXACT, int STAGE, bool EPI>
+__global__ void __launch_bounds__(kThreads, EPI ? 4 : 6)
 slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
                    const uint8_t* __restrict__ rec_slice, const int32_t* __restrict__ vid,
                    const int2* __restrict__ useg, const int* __restrict__ tile_off,
@@ -713,12 +713,12 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
   for (int r = g; r < rows; r += kThreads / 8) {
     const int64_t p = p0 + r;
     float4 s0 = zero, s1 = zero, t0 = zero, t1 = zero;
-    if (sub != nullptr) {
+    if (EPI && sub != nullptr) {
       const float* q = sub + p * sub_stride + c0 + 4 * l;
       if (on0) s0 = *reinterpret_cast<const float4*>(q);
       if (on1) s1 = *reinterpret_cast<const float4*>(q + 32);
     }
-    if (add != nullptr) {
+    if (EPI && add != nullptr) {
       const float* q = add + p * add_stride + c0 + 4 * l;
       if (on0) t0 = *reinterpret_cast<const float4*>(q);
       if (on1) t1 = *reinterpret_cast<const float4*>(q + 32);
@@ -752,13 +752,13 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
         fma4(a1, wi, x1);
       }
     }
-    if (sub != nullptr) {
+    if (EPI && sub != nullptr) {
       a0.x = __fsub_rn(a0.x, s0.x); a0.y = __fsub_rn(a0.y, s0.y);
       a0.z = __fsub_rn(a0.z, s0.z); a0.w = __fsub_rn(a0.w, s0.w);
       a1.x = __fsub_rn(a1.x, s1.x); a1.y = __fsub_rn(a1.y, s1.y);
       a1.z = __fsub_rn(a1.z, s1.z); a1.w = __fsub_rn(a1.w, s1.w);
     }
-    if (add != nullptr) {
+    if (EPI && add != nullptr) {
       a0.x = __fadd_rn(t0.x, a0.x); a0.y = __fadd_rn(t0.y, a0.y);
       a0.z = __fadd_rn(t0.z, a0.z); a0.w = __fadd_rn(t0.w, a0.w);
       a1.x = __fadd_rn(t1.x, a1.x); a1.y = __fadd_rn(t1.y, a1.y);
@@ -814,7 +814,7 @@ int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float*
 }
 
 namespace {
-template <bool EXACT, int STAGE>
+template <bool EXACT, int STAGE, bool EPI>
 int launch_slice(Lattice* L, const float* val, int Cc, float denom, float* dst, int64_t dst_stride,
                  const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
                  cudaStream_t st) {
@@ -822,12 +822,12 @@ int launch_slice(Lattice* L, const float* val, int Cc, float denom, float* dst, 
   const size_t smem = sizeof(float) * STAGE * kCW + sizeof(float2) * (size_t)kTile * d1;
   static bool attr_done = false;
   if (!attr_done) {
-    PL_CUDA(cudaFuncSetAttribute((slice_tiled_kernel<EXACT, STAGE>),
+    PL_CUDA(cudaFuncSetAttribute((slice_tiled_kernel<EXACT, STAGE, EPI>),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_done = true;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
-  PL_LAUNCH((slice_tiled_kernel<EXACT, STAGE>), grid, kThreads, smem, st, val, Cc, L->n, d1,
+  PL_LAUNCH((slice_tiled_kernel<EXACT, STAGE, EPI>), grid, kThreads, smem, st, val, Cc, L->n, d1,
             L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, dst, dst_stride, sub,
             sub_stride, add, add_stride);
   return PL_OK;
@@ -841,8 +841,12 @@ int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, i
     PL_CUDA(cudaEventSynchronize(L->max_U_ev));
     L->max_U = *L->h_max_U;
   }
-#define PL_SLICE(EX, ST) \
-  return launch_slice<EX, ST>(L, val, Cc, denom, dst, dst_stride, sub, sub_stride, add, add_stride, st)
+#define PL_SLICE(EX, ST)                                                                         \
+  return (sub != nullptr || add != nullptr)                                                      \
+             ? launch_slice<EX, ST, true>(L, val, Cc, denom, dst, dst_stride, sub, sub_stride,   \
+                                          add, add_stride, st)                                   \
+             : launch_slice<EX, ST, false>(L, val, Cc, denom, dst, dst_stride, sub, sub_stride,  \
+                                           add, add_stride, st)
   if (exact) {
     if (L->max_U <= 48) PL_SLICE(true, 48);
     if (L->max_U <= 96) PL_SLICE(true, 96);
