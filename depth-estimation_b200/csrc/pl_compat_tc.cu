@@ -3,22 +3,23 @@
 // for j < N output labels (N = L on one GPU, N = L / G when the labels are sharded over G ranks).
 //
 // crf/crf_module.py:99-102 with charb.forward (:71-75), pixel-major.  L is a multiple of 64
-// (128, 256, ...), N a multiple of 32, N <= 256 (TMEM accumulator columns).
+// (128, 256, ...), N a multiple of 32, N <= 256 (two TMEM accumulators of N columns).
 //
-// Two CTAs per SM, each warp-specialised and persistent over tiles of 128 pixels (= UMMA M);
-// while one CTA waits on HBM (statistics pass, epilogue stores) the other keeps the tensor pipe busy:
-//   warps 0-7  statistics: online softmax (row max, row sum) over all L labels, E from HBM,
-//              computed for tile t+1 while the MMAs of tile t drain;
-//              operand staging, per 32-label K chunk: re-read the E chunk (L2), Q = exp(-E - max) / sum,
-//              split Q = hi + lo (tf32) into the canonical K-major operand planes A (single buffer,
-//              handed over through mbarriers);
-//              epilogue: TMEM -> registers -> shared memory -> coalesced rows of P
-//   warp 8     one thread issues the MMAs: per 8-label K step three tcgen05.mma kind::tf32 of
-//              128 x N x 8 (lo*hi + hi*lo + hi*hi, fp32 parity, see pl_fused_tc.cu) into the
-//              128 x N fp32 accumulator in TMEM.  One instruction covers all N columns, so the A
-//              planes are read from shared memory once per pass, not once per 64-column block.
-//   warp 9     one thread streams the Mu records (pre-split hi / lo planes of Mu[:, 8 labels], one
-//              contiguous record per K step) through a ring of bulk TMA copies.
+// One persistent CTA per SM over tiles of 128 pixels (= UMMA M), four warp roles, everything
+// double-buffered so that the tensor pipe never waits for a phase of another role:
+//   warps 0-7   staging: per 32-label K chunk read the E chunk, Q' = exp(-E - rowmax) (the row sum
+//               is accumulated on the side and applied in the epilogue: one exp per value), split
+//               Q' = hi + lo (tf32) into the canonical K-major operand planes A[chunk & 1].  The row
+//               maxima of the NEXT tile are computed in the gaps (one 64-label step after every
+//               second chunk, loads issued a chunk ahead).
+//   warp 12     one thread issues the MMAs: per 8-label K step three tcgen05.mma kind::tf32 of
+//               128 x N x 8 (lo*hi + hi*lo + hi*hi, fp32 parity, see pl_fused_tc.cu) into the
+//               128 x N fp32 accumulator acc[tile & 1] in TMEM.
+//   warp 13     one thread streams the Mu records (pre-split hi / lo planes of Mu[:, 8 labels], one
+//               contiguous record per K step) through a ring of bulk TMA copies, and pulls the next
+//               tile's E rows into L2.
+//   warps 8-11  epilogue of tile t while the MMAs of tile t+1 run: TMEM -> registers (x scale /
+//               row sum) -> shared memory -> coalesced rows of P.
 //
 // E may be given in the BLOCKED layout an all-gather over label shards produces:
 // e[b][p][lw] with b < nblocks, lw < block_w, label = b * block_w + lw  (nblocks = 1: plain [n][L]).
@@ -33,19 +34,19 @@ namespace pl {
 namespace {
 
 constexpr int kTile = PL_TILE;  // 128
-constexpr int kSoft = 256;                       // threads of warps 0-7
-constexpr int kThreads = kSoft + 64;             // + MMA warp + TMA warp
+constexpr int kSoft = 256;                       // staging threads (warps 0-7)
+constexpr int kEpi = 128;                        // epilogue threads (warps 8-11)
+constexpr int kThreads = kSoft + kEpi + 64;      // + MMA warp + TMA warp
 constexpr int kKC = 32;                          // labels per A chunk
 constexpr int kKB = 8;                           // labels per Mu record (one MMA K step)
 constexpr int kA_CH = kTile * 16 + 16;           // bytes per 16-byte K chunk column of A
 constexpr int kA_BYTES = (kKC / 4) * kA_CH;      // one plane of A: 16512
+constexpr int kA_BUF = 2 * kA_BYTES;             // hi | lo
 constexpr int kPLD = 64 + 4;                     // epilogue staging pitch (floats)
-constexpr int kStageBytes = kTile * kPLD * 4;    // 34816 >= 2 * kA_BYTES; A planes and staging share it
+constexpr int kStageBytes = kTile * kPLD * 4;    // 34816
 constexpr int kMaxRing = 8;                      // Mu records in flight (TMA ring slots), at most
-constexpr int kRingBytes = 65 * 1024;            // ring budget: 4 slots at N = 256
+constexpr int kRingBytes = 97 * 1024;            // ring budget: 6 slots at N = 256
 constexpr int kMaxL = 512;
-
-static_assert(2 * kA_BYTES <= kStageBytes, "A planes must fit the staging region");
 
 __device__ int g_ctc_timeouts = 0;
 
@@ -73,6 +74,7 @@ __host__ __device__ constexpr int b_ch(int N) { return N * 16 + 16; }       // o
 __host__ __device__ constexpr int rec_bytes(int N) { return 4 * b_ch(N); }  // hi (2 columns) | lo (2 columns)
 
 __device__ __forceinline__ void bar_soft() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void bar_epi() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
 }
@@ -80,27 +82,30 @@ __device__ __forceinline__ void wait_or_count(uint64_t* bar, uint32_t parity) {
   if (!tc::mbar_wait(bar, parity)) atomicAdd(&g_ctc_timeouts, 1);
 }
 
-__global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
+__global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int REC = rec_bytes(a.N), BCH = b_ch(a.N);
-  unsigned char* s_a = smem;                              // A hi | lo planes; epilogue staging
-  unsigned char* s_b = smem + kStageBytes;                // ring of Mu records
-  float* s_m = reinterpret_cast<float*>(s_b + a.ring * REC);   // [2][128] row max of -E (this tile, next tile)
-  float* s_inv = s_m + 2 * kTile;                              // [128] 1 / row sum of this tile (+ 128 unused)
+  unsigned char* s_a = smem;                              // [2] A buffers: hi | lo planes
+  float* s_p = reinterpret_cast<float*>(smem + 2 * kA_BUF);   // epilogue staging
+  unsigned char* s_b = smem + 2 * kA_BUF + kStageBytes;   // ring of Mu records
+  float* s_m = reinterpret_cast<float*>(s_b + a.ring * REC);   // [2][128] row max of -E (tile parity)
+  float* s_inv = s_m + 2 * kTile;                              // [2][128] 1 / row sum (tile parity)
   int64_t* s_off = reinterpret_cast<int64_t*>(s_inv + 2 * kTile);   // [L/4] float4 group -> offset
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_off + kMaxL / 4);
   uint64_t* bar_full = bars;                  // [ring] Mu record landed
   uint64_t* bar_free = bars + kMaxRing;       // [ring] MMAs done with the record
-  uint64_t* bar_afull = bars + 2 * kMaxRing;  // A planes written (256 arrivals)
-  uint64_t* bar_afree = bar_afull + 1;        // MMAs done with the A planes
-  uint64_t* bar_acc = bar_afull + 2;          // tile's accumulator complete
-  uint64_t* bar_accfree = bar_afull + 3;      // epilogue has read the accumulator (256 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_afull + 4);
+  uint64_t* bar_afull = bars + 2 * kMaxRing;  // [2] A buffer written (256 arrivals)
+  uint64_t* bar_afree = bar_afull + 2;        // [2] MMAs done with the A buffer
+  uint64_t* bar_acc = bar_afull + 4;          // [2] accumulator complete
+  uint64_t* bar_accfree = bar_afull + 6;      // [2] epilogue has read the accumulator (128 arrivals)
+  uint64_t* bar_inv = bar_afull + 8;          // [2] row sums of the tile written (256 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_afull + 10);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int KCH = a.L / kKC;               // A chunks per tile
   const int steps_per_tile = a.L / kKB;    // Mu records per tile
-  const uint32_t tmem_cols = a.N <= 32 ? 32 : (a.N <= 64 ? 64 : (a.N <= 128 ? 128 : 256));
+  const uint32_t acc_cols = a.N <= 32 ? 32 : (a.N <= 64 ? 64 : (a.N <= 128 ? 128 : 256));
+  const uint32_t tmem_cols = 2 * acc_cols;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -108,10 +113,13 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
         tc::mbar_init(&bar_full[b], 1);
         tc::mbar_init(&bar_free[b], 1);
       }
-      tc::mbar_init(bar_afull, kSoft);
-      tc::mbar_init(bar_afree, 1);
-      tc::mbar_init(bar_acc, 1);
-      tc::mbar_init(bar_accfree, kSoft);
+      for (int b = 0; b < 2; b++) {
+        tc::mbar_init(&bar_afull[b], kSoft);
+        tc::mbar_init(&bar_afree[b], 1);
+        tc::mbar_init(&bar_acc[b], 1);
+        tc::mbar_init(&bar_accfree[b], kEpi);
+        tc::mbar_init(&bar_inv[b], kSoft);
+      }
       tc::fence_mbar_init();
     }
     __syncwarp();
@@ -132,7 +140,7 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
   const int64_t bw = a.block_w;
   const uint32_t my_tiles = (uint32_t)((a.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
 
-  if (warp == 9) {
+  if (warp == 13) {
     // ---- TMA producer: every tile consumes the same sequence of Mu records, the ring cycles ----
     if (lane == 0) {
       const uint32_t total = my_tiles * (uint32_t)steps_per_tile;
@@ -141,8 +149,8 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
       for (uint32_t t = 0; t < total; t++) {
         const uint32_t slot = t % a.ring, use = t / a.ring;
         if (rec < (uint32_t)a.nblocks && !a.use_blk && next_tile < a.ntiles) {
-          // pull block `rec` of the NEXT tile's E rows into L2: its statistics pass (a whole tile
-          // later) then runs at L2 latency.  Local memory only: peer blocks bypass the local L2.
+          // pull block `rec` of the NEXT tile's E rows into L2: its statistics steps (spread over
+          // this tile) then run at L2 latency.  Local memory only: peer blocks bypass the local L2.
           const int64_t q0 = next_tile * kTile;
           const int64_t nrows = min((int64_t)kTile, a.n - q0);
           const float* src = a.e + ((int64_t)rec * a.n + q0) * bw;
@@ -168,18 +176,19 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
         }
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == 12) {
     // ---- MMA issuer ------------------------------------------------------------------------
     if (lane == 0) {
       const uint32_t idesc = tc::idesc_tf32(kTile, a.N);
-      const uint32_t a_hi = tc::smem_u32(s_a), a_lo = a_hi + kA_BYTES;
-      uint32_t step = 0, a_cnt = 0;
+      uint32_t step = 0, g = 0;    // Mu records consumed, A chunks consumed
       for (uint32_t t = 0; t < my_tiles; t++) {
-        for (int kc = 0; kc < KCH; kc++) {
-          wait_or_count(bar_afull, a_cnt & 1);
-          a_cnt++;
-          if (kc == 0 && t > 0) wait_or_count(bar_accfree, (t - 1) & 1);
+        const uint32_t acc = tmem + (t & 1) * acc_cols;
+        for (int kc = 0; kc < KCH; kc++, g++) {
+          const uint32_t ab = g & 1;
+          wait_or_count(&bar_afull[ab], (g >> 1) & 1);
+          if (kc == 0 && t >= 2) wait_or_count(&bar_accfree[t & 1], ((t >> 1) - 1) & 1);
           tc::tcgen05_fence_after();
+          const uint32_t a_hi = tc::smem_u32(s_a + ab * kA_BUF), a_lo = a_hi + kA_BYTES;
           for (int j = 0; j < kKC / kKB; j++, step++) {
             const uint32_t slot = step % a.ring;
             wait_or_count(&bar_full[slot], (step / a.ring) & 1);
@@ -187,46 +196,93 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
             const uint32_t b_hi = tc::smem_u32(s_b + slot * REC), b_lo = b_hi + 2 * BCH;
 #pragma unroll
             for (int pass = 0; pass < 3; pass++) {  // lo*hi, hi*lo, hi*hi
-              const uint32_t ab = ((pass == 0) ? a_lo : a_hi) + j * 2 * kA_CH;
+              const uint32_t ab_addr = ((pass == 0) ? a_lo : a_hi) + j * 2 * kA_CH;
               const uint32_t bb = (pass == 1) ? b_lo : b_hi;
-              const uint64_t ad = tc::smem_desc_kmajor(ab, kA_CH, 128);
+              const uint64_t ad = tc::smem_desc_kmajor(ab_addr, kA_CH, 128);
               const uint64_t bd = tc::smem_desc_kmajor(bb, BCH, 128);
-              if (!(a.debug & 1)) tc::mma_tf32_ss(tmem, ad, bd, idesc, (kc | j | pass) != 0);
+              if (!(a.debug & 1)) tc::mma_tf32_ss(acc, ad, bd, idesc, (kc | j | pass) != 0);
             }
             tc::mma_commit(&bar_free[slot]);   // ring slot free once these MMAs have read it
           }
-          tc::mma_commit(bar_afree);           // A planes free
+          tc::mma_commit(&bar_afree[ab]);      // A buffer free
         }
-        tc::mma_commit(bar_acc);               // accumulator of this tile complete
+        tc::mma_commit(&bar_acc[t & 1]);       // accumulator of this tile complete
+      }
+    }
+  } else if (warp >= 8) {
+    // ---- warps 8-11: epilogue of tile t under the MMAs of tile t+1 ----------------------------
+    const int et = tid - kSoft;               // 0..127 = TMEM lane = pixel row of the tile
+    const int g = et >> 4, l = et & 15;       // copy-out: 16 lanes per row, 8 rows per pass
+    uint32_t t = 0;
+    for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, t++) {
+      const int64_t p0 = tile * kTile;
+      const int rows = (int)min((int64_t)kTile, a.n - p0);
+      const uint32_t par = (t >> 1) & 1;
+      wait_or_count(&bar_inv[t & 1], par);
+      const float* inv = s_inv + (t & 1) * kTile;
+      if (a.q_out != nullptr) {   // Q = exp / sum: rescale the rows written during staging (L2-hot)
+        for (int r = g; r < rows; r += kEpi / 16) {
+          const float ir = inv[r];
+          for (int c = 4 * l; c < a.L; c += 64) {
+            float4* qp = reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + c);
+            float4 x = *qp;
+            x.x *= ir; x.y *= ir; x.z *= ir; x.w *= ir;
+            *qp = x;
+          }
+        }
+      }
+      const float rscale = a.scale * inv[et];
+      wait_or_count(&bar_acc[t & 1], par);
+      tc::tcgen05_fence_after();
+      const uint32_t acc = tmem + (t & 1) * acc_cols + ((uint32_t)((warp & 3) * 32) << 16);
+      for (int c0 = 0; c0 < a.N; c0 += 64) {
+        const int cw = min(64, a.N - c0);          // 32 or 64
+        for (int c16 = 0; c16 < cw; c16 += 16) {
+          float v[16];
+          tc::tmem_ld_x16(acc + (uint32_t)(c0 + c16), v);
+#pragma unroll
+          for (int j = 0; j < 4; j++)
+            *reinterpret_cast<float4*>(s_p + et * kPLD + c16 + 4 * j) =
+                make_float4(v[4 * j] * rscale, v[4 * j + 1] * rscale, v[4 * j + 2] * rscale,
+                            v[4 * j + 3] * rscale);
+        }
+        if (c0 + 64 >= a.N) {      // last TMEM read of this tile: the accumulator may be overwritten
+          tc::tcgen05_fence_before();
+          mbar_arrive(&bar_accfree[t & 1]);
+        }
+        bar_epi();
+        if (4 * l < cw && !(a.debug & 8)) {
+#pragma unroll 4
+          for (int r = g; r < rows; r += kEpi / 16)
+            *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
+                *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
+        }
+        bar_epi();   // staging free again
       }
     }
   } else {
-    // ---- warps 0-7: statistics, operand staging, epilogue ------------------------------------
-    const int g = tid >> 4, l = tid & 15;     // statistics / copy-out: 16 lanes per row, 16 rows per pass
+    // ---- warps 0-7: operand staging + the next tile's row maxima -------------------------------
+    const int g = tid >> 4, l = tid & 15;     // statistics: 16 lanes per row, 16 rows per pass
     const int g2 = tid >> 3, l2 = tid & 7;    // staging: 8 lanes per row of a 32-label chunk, 32 rows per pass
     constexpr int RPT1 = kTile / (kSoft / 16);   // 8
     constexpr int RPT2 = kTile / (kSoft / 8);    // 4
+    const int SS = (a.debug & 4) ? 0 : a.L / 64;   // statistics steps per tile
 
-    // row maximum of -E over all L labels for the tile at p0 -> s_m[buf].  The row sum is
-    // accumulated while the operands are staged and applied in the epilogue (one exp per value).
-    auto statistics = [&](int64_t p0, int rows, int buf) {
-      float m[RPT1];
+    auto stat_load = [&](int64_t p0, int rows, int s, float4* e) {
+      const float* base = a.e + s_off[s * 16 + l] + p0 * bw;
 #pragma unroll
-      for (int i = 0; i < RPT1; i++) m[i] = -INFINITY;
-#pragma unroll 2
-      for (int s = 0; s < ((a.debug & 4) ? 0 : a.L / 64); s++) {
-        const float* base = a.e + s_off[s * 16 + l] + p0 * bw;
-        float4 e[RPT1];
-#pragma unroll
-        for (int i = 0; i < RPT1; i++) {
-          const int r = g + i * 16;
-          e[i] = (r < rows) ? *reinterpret_cast<const float4*>(base + r * bw)
-                            : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-        for (int i = 0; i < RPT1; i++)
-          m[i] = fmaxf(m[i], fmaxf(fmaxf(-e[i].x, -e[i].y), fmaxf(-e[i].z, -e[i].w)));
+      for (int i = 0; i < RPT1; i++) {
+        const int r = g + i * 16;
+        e[i] = (r < rows) ? *reinterpret_cast<const float4*>(base + r * bw)
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
       }
+    };
+    auto stat_max = [&](const float4* e, float* m) {
+#pragma unroll
+      for (int i = 0; i < RPT1; i++)
+        m[i] = fmaxf(m[i], fmaxf(fmaxf(-e[i].x, -e[i].y), fmaxf(-e[i].z, -e[i].w)));
+    };
+    auto stat_store = [&](const float* m, int buf) {
 #pragma unroll
       for (int i = 0; i < RPT1; i++) {
         float mi = m[i];
@@ -236,25 +292,41 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
       }
     };
 
-    uint32_t a_cnt = 0, t = 0;
-    {
+    // the first tile's row maxima, up front
+    if (blockIdx.x < a.ntiles) {
       const int64_t p0 = (int64_t)blockIdx.x * kTile;
-      if (blockIdx.x < a.ntiles) statistics(p0, (int)min((int64_t)kTile, a.n - p0), 0);
+      const int rows = (int)min((int64_t)kTile, a.n - p0);
+      float m[RPT1];
+#pragma unroll
+      for (int i = 0; i < RPT1; i++) m[i] = -INFINITY;
+      for (int s = 0; s < SS; s++) {
+        float4 e[RPT1];
+        stat_load(p0, rows, s, e);
+        stat_max(e, m);
+      }
+      stat_store(m, 0);
     }
     bar_soft();
+
+    uint32_t gch = 0, t = 0;   // A chunks produced, tiles done
     for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, t++) {
       const int64_t p0 = tile * kTile;
       const int rows = (int)min((int64_t)kTile, a.n - p0);
       const int buf = t & 1;
+      const int64_t np0 = (tile + gridDim.x) * kTile;
+      const bool has_next = tile + gridDim.x < a.ntiles;
+      const int nrows = has_next ? (int)min((int64_t)kTile, a.n - np0) : 0;
 
-      // ---- operand staging, K chunk by K chunk ----------------------------------------------
-      float rm[RPT2], rsum[RPT2];
+      float rm[RPT2], rsum[RPT2], mnext[RPT1];
 #pragma unroll
       for (int i = 0; i < RPT2; i++) {
         rm[i] = s_m[buf * kTile + g2 + i * 32];
         rsum[i] = 0.f;
       }
-      float4 ec[RPT2], en[RPT2];
+#pragma unroll
+      for (int i = 0; i < RPT1; i++) mnext[i] = -INFINITY;
+
+      float4 ec[RPT2], en[RPT2], es[RPT1];
       auto load_chunk = [&](int kc, float4* e) {
         const float* base = a.e + s_off[kc * 8 + l2] + p0 * bw;
 #pragma unroll
@@ -265,10 +337,15 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
         }
       };
       load_chunk(0, ec);
-      for (int kc = 0; kc < KCH; kc++) {
-        // the next chunk's E values first: the loads overlap the MMAs still reading the A planes
+      for (int kc = 0; kc < KCH; kc++, gch++) {
+        // loads first: the next chunk of this tile and, every second chunk, one 64-label step of
+        // the next tile's row maxima; they complete under the waits and the exps below
         if (kc + 1 < KCH) load_chunk(kc + 1, en);
-        if (a_cnt > 0) wait_or_count(bar_afree, (a_cnt - 1) & 1);
+        const bool stat = has_next && !(kc & 1) && (kc >> 1) < SS;
+        if (stat) stat_load(np0, nrows, kc >> 1, es);
+        const uint32_t ab = gch & 1;
+        if (gch >= 2) wait_or_count(&bar_afree[ab], ((gch >> 1) - 1) & 1);
+        unsigned char* abuf = s_a + ab * kA_BUF;
 #pragma unroll
         for (int i = 0; i < RPT2; i++) {
           const int r = g2 + i * 32;
@@ -279,7 +356,7 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
             x.z = __expf(-ec[i].z - rm[i]);
             x.w = __expf(-ec[i].w - rm[i]);
             rsum[i] += (x.x + x.y) + (x.z + x.w);
-            if (a.q_out != nullptr)   // unnormalised here, scaled by 1 / sum after the tile
+            if (a.q_out != nullptr)   // unnormalised here, scaled by 1 / sum by the epilogue warps
               *reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + kc * kKC + 4 * l2) = x;
           }
           float4 hi, lo;
@@ -287,80 +364,27 @@ __global__ void __launch_bounds__(kThreads, 2) compat_tc_kernel(const CArgs a) {
           hi.y = tc::tf32_rna(x.y); lo.y = tc::tf32_rna(x.y - hi.y);
           hi.z = tc::tf32_rna(x.z); lo.z = tc::tf32_rna(x.z - hi.z);
           hi.w = tc::tf32_rna(x.w); lo.w = tc::tf32_rna(x.w - hi.w);
-          unsigned char* pa = s_a + l2 * kA_CH + r * 16;
+          unsigned char* pa = abuf + l2 * kA_CH + r * 16;
           *reinterpret_cast<float4*>(pa) = hi;
           *reinterpret_cast<float4*>(pa + kA_BYTES) = lo;
         }
         tc::fence_proxy_async();
-        mbar_arrive(bar_afull);
-        a_cnt++;
+        mbar_arrive(&bar_afull[ab]);
+        if (stat) stat_max(es, mnext);
 #pragma unroll
         for (int i = 0; i < RPT2; i++) ec[i] = en[i];
       }
-
-      // row sums: combine the 8 lanes of a row
+      // row sums of this tile -> epilogue warps; row maxima of the next tile -> ourselves
 #pragma unroll
       for (int i = 0; i < RPT2; i++) {
         float si = rsum[i];
 #pragma unroll
         for (int o = 4; o > 0; o >>= 1) si += __shfl_xor_sync(0xffffffffu, si, o, 8);
-        if (l2 == 0) s_inv[g2 + i * 32] = (g2 + i * 32 < rows) ? __fdividef(1.0f, si) : 0.f;
+        if (l2 == 0) s_inv[buf * kTile + g2 + i * 32] = (g2 + i * 32 < rows) ? __fdividef(1.0f, si) : 0.f;
       }
-
-      // ---- the next tile's statistics, while this tile's last MMAs drain ----------------------
-      {
-        const int64_t nt = tile + gridDim.x;
-        if (nt < a.ntiles) statistics(nt * kTile, (int)min((int64_t)kTile, a.n - nt * kTile), buf ^ 1);
-      }
-
-      // ---- epilogue: per 64-column block TMEM -> staging -> coalesced rows of P ----------------
-      bar_soft();   // row sums visible
-      if (a.q_out != nullptr) {   // Q = exp / sum: rescale the rows written during staging (L2-hot)
-        for (int i = 0; i < RPT1; i++) {
-          const int r = g + i * 16;
-          if (r >= rows) continue;
-          const float inv = s_inv[r];
-          for (int c = 4 * l; c < a.L; c += 64) {
-            float4* qp = reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + c);
-            float4 x = *qp;
-            x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
-            *qp = x;
-          }
-        }
-      }
-      wait_or_count(bar_acc, t & 1);
-      tc::tcgen05_fence_after();
-      float* s_p = reinterpret_cast<float*>(s_a);
-      const int q = warp & 3, hsel = warp >> 2;    // TMEM lane quarter; column half of the block
-      const int row = q * 32 + lane;
-      const float rscale = a.scale * s_inv[row];
-      for (int c0 = 0; c0 < a.N; c0 += 64) {
-        const int cw = min(64, a.N - c0);          // 32 or 64
-        const int cpw = cw >> 1;                   // columns per warp: 16 or 32
-        for (int c16 = 0; c16 < cpw / 16; c16++) {
-          const int col = hsel * cpw + c16 * 16;
-          float v[16];
-          tc::tmem_ld_x16(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(c0 + col), v);
-#pragma unroll
-          for (int j = 0; j < 4; j++)
-            *reinterpret_cast<float4*>(s_p + row * kPLD + col + 4 * j) =
-                make_float4(v[4 * j] * rscale, v[4 * j + 1] * rscale, v[4 * j + 2] * rscale,
-                            v[4 * j + 3] * rscale);
-        }
-        if (c0 + 64 >= a.N) {      // last TMEM read of this tile: the accumulator may be overwritten
-          tc::tcgen05_fence_before();
-          mbar_arrive(bar_accfree);
-        }
-        bar_soft();
-#pragma unroll
-        for (int i = 0; i < RPT1; i++) {
-          const int r = g + i * 16;
-          if (r < rows && 4 * l < cw && !(a.debug & 8))
-            *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
-                *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
-        }
-        bar_soft();   // staging (= A planes) free again; also publishes the next tile's statistics
-      }
+      mbar_arrive(&bar_inv[buf]);
+      if (has_next) stat_store(mnext, buf ^ 1);
+      bar_soft();
     }
   }
 
@@ -401,8 +425,8 @@ int ring_slots(int N) {
 }
 
 size_t ctc_smem(int N) {
-  return (size_t)kStageBytes + (size_t)ring_slots(N) * rec_bytes(N) + 4 * kTile * 4 +
-         (kMaxL / 4) * 8 + (2 * kMaxRing + 4) * 8 + 16;
+  return 2 * (size_t)kA_BUF + kStageBytes + (size_t)ring_slots(N) * rec_bytes(N) + 4 * kTile * 4 +
+         (kMaxL / 4) * 8 + (2 * kMaxRing + 10) * 8 + 16;
 }
 
 }  // namespace
@@ -444,10 +468,10 @@ int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_re
   static bool done = false;
   if (!done) {
     PL_CUDA(cudaFuncSetAttribute(compat_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 110 * 1024));   // two CTAs per SM; ctc_smem(N) <= 104.2 KB for every N
+                                 210 * 1024));   // one CTA per SM; ctc_smem(N) <= 203 KB for every N
     done = true;
   }
-  const int64_t cap = 2 * PL_SM_COUNT;
+  const int64_t cap = PL_SM_COUNT;
   const unsigned grid = (unsigned)(a.ntiles < cap ? a.ntiles : cap);
   PL_LAUNCH(compat_tc_kernel, grid, kThreads, smem, st, a);
   return PL_OK;
