@@ -7,18 +7,18 @@
 //
 // One persistent CTA per SM over tiles of 128 pixels (= UMMA M), four warp roles, everything
 // double-buffered so that the tensor pipe never waits for a phase of another role:
-//   warps 0-7   staging: per 32-label K chunk read the E chunk, Q' = exp(-E - rowmax) (the row sum
+//   warps 0-15  staging: per 32-label K chunk read the E chunk, Q' = exp(-E - rowmax) (the row sum
 //               is accumulated on the side and applied in the epilogue: one exp per value), split
 //               Q' = hi + lo (tf32) into the canonical K-major operand planes A[chunk & 1].  The row
 //               maxima of the NEXT tile are computed in the gaps (one 64-label step after every
 //               second chunk, loads issued a chunk ahead).
-//   warp 12     one thread issues the MMAs: per 8-label K step three tcgen05.mma kind::tf32 of
+//   warp 20     one thread issues the MMAs: per 8-label K step three tcgen05.mma kind::tf32 of
 //               128 x N x 8 (lo*hi + hi*lo + hi*hi, fp32 parity, see pl_fused_tc.cu) into the
 //               128 x N fp32 accumulator acc[tile & 1] in TMEM.
-//   warp 13     one thread streams the Mu records (pre-split hi / lo planes of Mu[:, 8 labels], one
+//   warp 21     one thread streams the Mu records (pre-split hi / lo planes of Mu[:, 8 labels], one
 //               contiguous record per K step) through a ring of bulk TMA copies, and pulls the next
 //               tile's E rows into L2.
-//   warps 8-11  epilogue of tile t while the MMAs of tile t+1 run: TMEM -> registers (x scale /
+//   warps 16-19 epilogue of tile t while the MMAs of tile t+1 run: TMEM -> registers (x scale /
 //               row sum) -> shared memory -> coalesced rows of P.
 //
 // E may be given in the BLOCKED layout an all-gather over label shards produces:
@@ -34,18 +34,18 @@ namespace pl {
 namespace {
 
 constexpr int kTile = PL_TILE;  // 128
-constexpr int kSoft = 256;                       // staging threads (warps 0-7)
-constexpr int kEpi = 128;                        // epilogue threads (warps 8-11)
+constexpr int kSoft = 512;                       // staging threads (warps 0-15)
+constexpr int kEpi = 128;                        // epilogue threads (warps 16-19)
 constexpr int kThreads = kSoft + kEpi + 64;      // + MMA warp + TMA warp
 constexpr int kKC = 32;                          // labels per A chunk
-constexpr int kKB = 8;                           // labels per Mu record (one MMA K step)
+constexpr int kKB = 16;                          // labels per Mu record (two MMA K steps)
 constexpr int kA_CH = kTile * 16 + 16;           // bytes per 16-byte K chunk column of A
 constexpr int kA_BYTES = (kKC / 4) * kA_CH;      // one plane of A: 16512
 constexpr int kA_BUF = 2 * kA_BYTES;             // hi | lo
 constexpr int kPLD = 64 + 4;                     // epilogue staging pitch (floats)
 constexpr int kStageBytes = kTile * kPLD * 4;    // 34816
 constexpr int kMaxRing = 8;                      // Mu records in flight (TMA ring slots), at most
-constexpr int kRingBytes = 97 * 1024;            // ring budget: 6 slots at N = 256
+constexpr int kRingBytes = 97 * 1024;            // ring budget: 3 slots at N = 256
 constexpr int kMaxL = 512;
 
 __device__ int g_ctc_timeouts = 0;
@@ -67,22 +67,38 @@ struct CArgs {
   int L, N;
   int ring;             // ring slots
   float scale;
-  int debug;  // timing experiments only: 1 = no MMAs, 2 = no Mu copies, 4 = no statistics loads, 8 = no P stores
+  int debug;  // PL_CTC_DEBUG, timing experiments only: 1 = no MMAs, 2 = no Mu copies, 4 = no statistics loads,
+              // 8 = no P stores, 32 = no staging loads, 64 = no L2 prefetch, 128 = print per-role wait cycles
 };
 
 __host__ __device__ constexpr int b_ch(int N) { return N * 16 + 16; }       // one K chunk column of B
-__host__ __device__ constexpr int rec_bytes(int N) { return 4 * b_ch(N); }  // hi (2 columns) | lo (2 columns)
+__host__ __device__ constexpr int rec_bytes(int N) { return 2 * (kKB / 4) * b_ch(N); }  // hi (4 columns) | lo (4 columns)
 
-__device__ __forceinline__ void bar_soft() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void bar_soft() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 __device__ __forceinline__ void bar_epi() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float tf32_cut(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
 __device__ __forceinline__ void wait_or_count(uint64_t* bar, uint32_t parity) {
   if (!tc::mbar_wait(bar, parity)) atomicAdd(&g_ctc_timeouts, 1);
 }
 
+#define TWAIT(acc, bar, par)                    \
+  do {                                          \
+    const long long _t0 = clock64();            \
+    wait_or_count((bar), (par));                \
+    (acc) += clock64() - _t0;                   \
+  } while (0)
+
 __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
+  long long tw0 = 0, tw1 = 0, tw2 = 0;   // PL_CTC_DEBUG=128: cycles each role spends waiting
+  const long long t_begin = clock64();
   extern __shared__ __align__(128) unsigned char smem[];
   const int REC = rec_bytes(a.N), BCH = b_ch(a.N);
   unsigned char* s_a = smem;                              // [2] A buffers: hi | lo planes
@@ -94,11 +110,11 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_off + kMaxL / 4);
   uint64_t* bar_full = bars;                  // [ring] Mu record landed
   uint64_t* bar_free = bars + kMaxRing;       // [ring] MMAs done with the record
-  uint64_t* bar_afull = bars + 2 * kMaxRing;  // [2] A buffer written (256 arrivals)
+  uint64_t* bar_afull = bars + 2 * kMaxRing;  // [2] A buffer written (one arrival per staging warp)
   uint64_t* bar_afree = bar_afull + 2;        // [2] MMAs done with the A buffer
   uint64_t* bar_acc = bar_afull + 4;          // [2] accumulator complete
   uint64_t* bar_accfree = bar_afull + 6;      // [2] epilogue has read the accumulator (128 arrivals)
-  uint64_t* bar_inv = bar_afull + 8;          // [2] row sums of the tile written (256 arrivals)
+  uint64_t* bar_inv = bar_afull + 8;          // [2] row sums of the tile written (kSoft arrivals)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_afull + 10);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -114,7 +130,7 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         tc::mbar_init(&bar_free[b], 1);
       }
       for (int b = 0; b < 2; b++) {
-        tc::mbar_init(&bar_afull[b], kSoft);
+        tc::mbar_init(&bar_afull[b], kSoft / 32);   // one elected arrival per staging warp
         tc::mbar_init(&bar_afree[b], 1);
         tc::mbar_init(&bar_acc[b], 1);
         tc::mbar_init(&bar_accfree[b], kEpi);
@@ -140,85 +156,109 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
   const int64_t bw = a.block_w;
   const uint32_t my_tiles = (uint32_t)((a.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
 
-  if (warp == 13) {
+  if (warp == kSoft / 32 + 5) {
     // ---- TMA producer: every tile consumes the same sequence of Mu records, the ring cycles ----
     if (lane == 0) {
       const uint32_t total = my_tiles * (uint32_t)steps_per_tile;
-      uint32_t rec = 0;
+      uint32_t rec = 0, slot = 0, phase = 1;   // phase: parity of the slot's PREVIOUS use (fresh barrier: 1 passes)
       int64_t next_tile = (int64_t)blockIdx.x + gridDim.x;
+      const uint8_t* src_rec = a.mu_rec;
       for (uint32_t t = 0; t < total; t++) {
-        const uint32_t slot = t % a.ring, use = t / a.ring;
-        if (rec < (uint32_t)a.nblocks && !a.use_blk && next_tile < a.ntiles) {
-          // pull block `rec` of the NEXT tile's E rows into L2: its statistics steps (spread over
-          // this tile) then run at L2 latency.  Local memory only: peer blocks bypass the local L2.
+        if (rec == 0 && !a.use_blk && next_tile < a.ntiles && !(a.debug & 64)) {
+          // pull the NEXT tile's E rows into L2: its statistics steps (spread over this tile) then
+          // run at L2 latency.  Local memory only: peer blocks bypass the local L2.
           const int64_t q0 = next_tile * kTile;
-          const int64_t nrows = min((int64_t)kTile, a.n - q0);
-          const float* src = a.e + ((int64_t)rec * a.n + q0) * bw;
-          const uint32_t bytes = (uint32_t)(nrows * bw * 4);
-          for (uint32_t o = 0; o < bytes; o += 16384) {
-            const uint32_t sz = min(16384u, bytes - o);
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(
-                             reinterpret_cast<const char*>(src) + o),
-                         "r"(sz)
-                         : "memory");
+          const uint32_t bytes = (uint32_t)(min((int64_t)kTile, a.n - q0) * bw * 4);
+          for (int b = 0; b < a.nblocks; b++) {
+            const char* src = reinterpret_cast<const char*>(a.e + ((int64_t)b * a.n + q0) * bw);
+            for (uint32_t o = 0; o < bytes; o += 32768)
+              asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src + o),
+                           "r"(min(32768u, bytes - o))
+                           : "memory");
           }
         }
-        if (use > 0) wait_or_count(&bar_free[slot], (use - 1) & 1);
+        TWAIT(tw0, &bar_free[slot], phase);
         if (a.debug & 2) {
           mbar_arrive(&bar_full[slot]);
         } else {
           tc::mbar_arrive_expect_tx(&bar_full[slot], REC);
-          tc::tma_load_1d(s_b + slot * REC, a.mu_rec + (size_t)rec * REC, REC, &bar_full[slot]);
+          tc::tma_load_1d(s_b + slot * REC, src_rec, REC, &bar_full[slot]);
         }
+        src_rec += REC;
         if (++rec == (uint32_t)steps_per_tile) {
           rec = 0;
+          src_rec = a.mu_rec;
           next_tile += gridDim.x;
         }
+        if (++slot == (uint32_t)a.ring) {
+          slot = 0;
+          phase ^= 1;
+        }
       }
+      if ((a.debug & 128) && blockIdx.x == 0)
+        printf("tma: total %lld wait_free %lld\n", clock64() - t_begin, tw0);
     }
-  } else if (warp == 12) {
+  } else if (warp == kSoft / 32 + 4) {
     // ---- MMA issuer ------------------------------------------------------------------------
     if (lane == 0) {
       const uint32_t idesc = tc::idesc_tf32(kTile, a.N);
-      uint32_t step = 0, g = 0;    // Mu records consumed, A chunks consumed
+      // descriptors are built once; an operand further on is the same descriptor plus (bytes >> 4)
+      // in the 14-bit address field (shared memory is < 256 KB: no carry out of the field)
+      const uint64_t a_desc0 = tc::smem_desc_kmajor(tc::smem_u32(s_a), kA_CH, 128);
+      const uint64_t b_desc0 = tc::smem_desc_kmajor(tc::smem_u32(s_b), BCH, 128);
+      const uint64_t a_lo_off = kA_BYTES >> 4, a_buf_off = kA_BUF >> 4, a_k8 = (2 * kA_CH) >> 4;
+      const uint64_t b_lo_off = ((kKB / 4) * BCH) >> 4, b_k8 = (2 * BCH) >> 4, b_slot = REC >> 4;
+      uint32_t slot = 0, phase = 0, g = 0;    // ring slot + parity of its current use, A chunks consumed
+      uint64_t b_cur = b_desc0;
       for (uint32_t t = 0; t < my_tiles; t++) {
         const uint32_t acc = tmem + (t & 1) * acc_cols;
         for (int kc = 0; kc < KCH; kc++, g++) {
           const uint32_t ab = g & 1;
-          wait_or_count(&bar_afull[ab], (g >> 1) & 1);
-          if (kc == 0 && t >= 2) wait_or_count(&bar_accfree[t & 1], ((t >> 1) - 1) & 1);
+          TWAIT(tw0, &bar_afull[ab], (g >> 1) & 1);
+          if (kc == 0 && t >= 2) TWAIT(tw1, &bar_accfree[t & 1], ((t >> 1) - 1) & 1);
           tc::tcgen05_fence_after();
-          const uint32_t a_hi = tc::smem_u32(s_a + ab * kA_BUF), a_lo = a_hi + kA_BYTES;
-          for (int j = 0; j < kKC / kKB; j++, step++) {
-            const uint32_t slot = step % a.ring;
-            wait_or_count(&bar_full[slot], (step / a.ring) & 1);
-            tc::tcgen05_fence_after();
-            const uint32_t b_hi = tc::smem_u32(s_b + slot * REC), b_lo = b_hi + 2 * BCH;
+          const uint64_t a_cur = a_desc0 + ab * a_buf_off;
 #pragma unroll
-            for (int pass = 0; pass < 3; pass++) {  // lo*hi, hi*lo, hi*hi
-              const uint32_t ab_addr = ((pass == 0) ? a_lo : a_hi) + j * 2 * kA_CH;
-              const uint32_t bb = (pass == 1) ? b_lo : b_hi;
-              const uint64_t ad = tc::smem_desc_kmajor(ab_addr, kA_CH, 128);
-              const uint64_t bd = tc::smem_desc_kmajor(bb, BCH, 128);
-              if (!(a.debug & 1)) tc::mma_tf32_ss(acc, ad, bd, idesc, (kc | j | pass) != 0);
+          for (int j = 0; j < kKC / kKB; j++) {
+            TWAIT(tw2, &bar_full[slot], phase);
+            tc::tcgen05_fence_after();
+            if (!(a.debug & 1)) {
+#pragma unroll
+              for (int ks = 0; ks < kKB / 8; ks++) {
+                const uint64_t ad = a_cur + (uint64_t)(j * (kKB / 8) + ks) * a_k8;
+                const uint64_t bd = b_cur + (uint64_t)ks * b_k8;
+                // lo*hi, hi*lo, hi*hi
+                tc::mma_tf32_ss(acc, ad + a_lo_off, bd, idesc, (kc | j | ks) != 0);
+                tc::mma_tf32_ss(acc, ad, bd + b_lo_off, idesc, true);
+                tc::mma_tf32_ss(acc, ad, bd, idesc, true);
+              }
             }
             tc::mma_commit(&bar_free[slot]);   // ring slot free once these MMAs have read it
+            b_cur += b_slot;
+            if (++slot == (uint32_t)a.ring) {
+              slot = 0;
+              phase ^= 1;
+              b_cur = b_desc0;
+            }
           }
           tc::mma_commit(&bar_afree[ab]);      // A buffer free
         }
         tc::mma_commit(&bar_acc[t & 1]);       // accumulator of this tile complete
       }
+      if ((a.debug & 128) && blockIdx.x == 0)
+        printf("mma: total %lld wait_afull %lld wait_accfree %lld wait_bfull %lld tiles %u\n",
+               clock64() - t_begin, tw0, tw1, tw2, my_tiles);
     }
-  } else if (warp >= 8) {
-    // ---- warps 8-11: epilogue of tile t under the MMAs of tile t+1 ----------------------------
-    const int et = tid - kSoft;               // 0..127 = TMEM lane = pixel row of the tile
+  } else if (warp >= kSoft / 32) {
+    // ---- warps 16-19: epilogue of tile t under the MMAs of tile t+1 ----------------------------
+    const int et = tid - kSoft;               // 0..127 = TMEM lane = pixel row of the tile (warp 16 + q -> lanes 32q..)
     const int g = et >> 4, l = et & 15;       // copy-out: 16 lanes per row, 8 rows per pass
     uint32_t t = 0;
     for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, t++) {
       const int64_t p0 = tile * kTile;
       const int rows = (int)min((int64_t)kTile, a.n - p0);
       const uint32_t par = (t >> 1) & 1;
-      wait_or_count(&bar_inv[t & 1], par);
+      TWAIT(tw0, &bar_inv[t & 1], par);
       const float* inv = s_inv + (t & 1) * kTile;
       if (a.q_out != nullptr) {   // Q = exp / sum: rescale the rows written during staging (L2-hot)
         for (int r = g; r < rows; r += kEpi / 16) {
@@ -232,7 +272,7 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         }
       }
       const float rscale = a.scale * inv[et];
-      wait_or_count(&bar_acc[t & 1], par);
+      TWAIT(tw1, &bar_acc[t & 1], par);
       tc::tcgen05_fence_after();
       const uint32_t acc = tmem + (t & 1) * acc_cols + ((uint32_t)((warp & 3) * 32) << 16);
       for (int c0 = 0; c0 < a.N; c0 += 64) {
@@ -252,7 +292,7 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         }
         bar_epi();
         if (4 * l < cw && !(a.debug & 8)) {
-#pragma unroll 4
+#pragma unroll 8
           for (int r = g; r < rows; r += kEpi / 16)
             *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
                 *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
@@ -260,10 +300,12 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         bar_epi();   // staging free again
       }
     }
+    if ((a.debug & 128) && blockIdx.x == 0 && et == 0)
+      printf("epi: total %lld wait_inv %lld wait_acc %lld\n", clock64() - t_begin, tw0, tw1);
   } else {
-    // ---- warps 0-7: operand staging + the next tile's row maxima -------------------------------
-    const int g = tid >> 4, l = tid & 15;     // statistics: 16 lanes per row, 16 rows per pass
-    const int g2 = tid >> 3, l2 = tid & 7;    // staging: 8 lanes per row of a 32-label chunk, 32 rows per pass
+    // ---- warps 0-15: operand staging + the next tile's row maxima -------------------------------
+    const int g = tid >> 4, l = tid & 15;     // statistics: 16 lanes per row, 32 rows per pass
+    const int g2 = tid >> 3, l2 = tid & 7;    // staging: 8 lanes per row of a 32-label chunk, 64 rows per pass
     constexpr int RPT1 = kTile / (kSoft / 16);   // 8
     constexpr int RPT2 = kTile / (kSoft / 8);    // 4
     const int SS = (a.debug & 4) ? 0 : a.L / 64;   // statistics steps per tile
@@ -272,7 +314,7 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
       const float* base = a.e + s_off[s * 16 + l] + p0 * bw;
 #pragma unroll
       for (int i = 0; i < RPT1; i++) {
-        const int r = g + i * 16;
+        const int r = g + i * (kSoft / 16);
         e[i] = (r < rows) ? *reinterpret_cast<const float4*>(base + r * bw)
                           : make_float4(0.f, 0.f, 0.f, 0.f);
       }
@@ -288,7 +330,7 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         float mi = m[i];
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) mi = fmaxf(mi, __shfl_xor_sync(0xffffffffu, mi, o, 16));
-        if (l == 0) s_m[buf * kTile + g + i * 16] = mi;
+        if (l == 0) s_m[buf * kTile + g + i * (kSoft / 16)] = mi;
       }
     };
 
@@ -320,7 +362,7 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
       float rm[RPT2], rsum[RPT2], mnext[RPT1];
 #pragma unroll
       for (int i = 0; i < RPT2; i++) {
-        rm[i] = s_m[buf * kTile + g2 + i * 32];
+        rm[i] = -1.4426950408889634f * s_m[buf * kTile + g2 + i * (kSoft / 8)];   // exp(-e - m) = 2^(-e log2e - m log2e)
         rsum[i] = 0.f;
       }
 #pragma unroll
@@ -331,46 +373,48 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         const float* base = a.e + s_off[kc * 8 + l2] + p0 * bw;
 #pragma unroll
         for (int i = 0; i < RPT2; i++) {
-          const int r = g2 + i * 32;
-          e[i] = (r < rows) ? *reinterpret_cast<const float4*>(base + r * bw)
-                            : make_float4(0.f, 0.f, 0.f, 0.f);
+          const int r = g2 + i * (kSoft / 8);
+          e[i] = (r < rows && !(a.debug & 32)) ? *reinterpret_cast<const float4*>(base + r * bw)
+                                                : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       };
       load_chunk(0, ec);
       for (int kc = 0; kc < KCH; kc++, gch++) {
-        // loads first: the next chunk of this tile and, every second chunk, one 64-label step of
-        // the next tile's row maxima; they complete under the waits and the exps below
         if (kc + 1 < KCH) load_chunk(kc + 1, en);
+        // every second chunk one 64-label step of the next tile's row maxima; the loads complete
+        // under the waits and the exps below
         const bool stat = has_next && !(kc & 1) && (kc >> 1) < SS;
         if (stat) stat_load(np0, nrows, kc >> 1, es);
         const uint32_t ab = gch & 1;
-        if (gch >= 2) wait_or_count(&bar_afree[ab], ((gch >> 1) - 1) & 1);
+        if (gch >= 2) TWAIT(tw0, &bar_afree[ab], ((gch >> 1) - 1) & 1);
         unsigned char* abuf = s_a + ab * kA_BUF;
 #pragma unroll
         for (int i = 0; i < RPT2; i++) {
-          const int r = g2 + i * 32;
+          const int r = g2 + i * (kSoft / 8);
           float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
           if (r < rows) {
-            x.x = __expf(-ec[i].x - rm[i]);
-            x.y = __expf(-ec[i].y - rm[i]);
-            x.z = __expf(-ec[i].z - rm[i]);
-            x.w = __expf(-ec[i].w - rm[i]);
+            x.x = ex2_fast(fmaf(ec[i].x, -1.4426950408889634f, rm[i]));
+            x.y = ex2_fast(fmaf(ec[i].y, -1.4426950408889634f, rm[i]));
+            x.z = ex2_fast(fmaf(ec[i].z, -1.4426950408889634f, rm[i]));
+            x.w = ex2_fast(fmaf(ec[i].w, -1.4426950408889634f, rm[i]));
             rsum[i] += (x.x + x.y) + (x.z + x.w);
             if (a.q_out != nullptr)   // unnormalised here, scaled by 1 / sum by the epilogue warps
               *reinterpret_cast<float4*>(a.q_out + (p0 + r) * a.L + kc * kKC + 4 * l2) = x;
           }
           float4 hi, lo;
-          hi.x = tc::tf32_rna(x.x); lo.x = tc::tf32_rna(x.x - hi.x);
-          hi.y = tc::tf32_rna(x.y); lo.y = tc::tf32_rna(x.y - hi.y);
-          hi.z = tc::tf32_rna(x.z); lo.z = tc::tf32_rna(x.z - hi.z);
-          hi.w = tc::tf32_rna(x.w); lo.w = tc::tf32_rna(x.w - hi.w);
+          // hi = x cut to tf32 (the MMA reads only the top 19 bits anyway), lo = x - hi exactly
+          hi.x = tf32_cut(x.x); lo.x = x.x - hi.x;
+          hi.y = tf32_cut(x.y); lo.y = x.y - hi.y;
+          hi.z = tf32_cut(x.z); lo.z = x.z - hi.z;
+          hi.w = tf32_cut(x.w); lo.w = x.w - hi.w;
           unsigned char* pa = abuf + l2 * kA_CH + r * 16;
           *reinterpret_cast<float4*>(pa) = hi;
           *reinterpret_cast<float4*>(pa + kA_BYTES) = lo;
         }
         tc::fence_proxy_async();
-        mbar_arrive(&bar_afull[ab]);
-        if (stat) stat_max(es, mnext);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_afull[ab]);
+        if ((kc & 1) && has_next && (kc >> 1) < SS) stat_max(es, mnext);   // requested a chunk ago
 #pragma unroll
         for (int i = 0; i < RPT2; i++) ec[i] = en[i];
       }
@@ -380,12 +424,18 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         float si = rsum[i];
 #pragma unroll
         for (int o = 4; o > 0; o >>= 1) si += __shfl_xor_sync(0xffffffffu, si, o, 8);
-        if (l2 == 0) s_inv[buf * kTile + g2 + i * 32] = (g2 + i * 32 < rows) ? __fdividef(1.0f, si) : 0.f;
+        if (l2 == 0) s_inv[buf * kTile + g2 + i * (kSoft / 8)] = (g2 + i * (kSoft / 8) < rows) ? __fdividef(1.0f, si) : 0.f;
       }
       mbar_arrive(&bar_inv[buf]);
       if (has_next) stat_store(mnext, buf ^ 1);
-      bar_soft();
+      {
+        const long long _t0 = clock64();
+        bar_soft();
+        tw2 += clock64() - _t0;
+      }
     }
+    if ((a.debug & 128) && blockIdx.x == 0 && tid == 0)
+      printf("stage: total %lld wait_afree %lld wait_bar %lld\n", clock64() - t_begin, tw0, tw2);
   }
 
   __syncthreads();
@@ -395,13 +445,13 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
   }
 }
 
-// Mu[l0 + j][kb*8 + k] = muT[(kb*8 + k) * L + l0 + j]  ->  record kb: hi plane | lo plane, each two
-// 16-byte K chunk columns of N rows (+ 16 bytes of pad) in the canonical K-major layout.
+// Mu[l0 + j][kb*16 + k] = muT[(kb*16 + k) * L + l0 + j]  ->  record kb: hi plane | lo plane, each
+// four 16-byte K chunk columns of N rows (+ 16 bytes of pad) in the canonical K-major layout.
 __global__ void __launch_bounds__(256)
 mu_records_kernel(const float* __restrict__ muT, int L, int l0, int N, uint8_t* __restrict__ out) {
   const int nrec = L / kKB;
   const int chunk_floats = b_ch(N) / 4;
-  const int plane_floats = 2 * chunk_floats;
+  const int plane_floats = (kKB / 4) * chunk_floats;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nrec * plane_floats;
        i += gridDim.x * blockDim.x) {
     const int kb = i / plane_floats, w = i - kb * plane_floats;
@@ -468,7 +518,7 @@ int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_re
   static bool done = false;
   if (!done) {
     PL_CUDA(cudaFuncSetAttribute(compat_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 210 * 1024));   // one CTA per SM; ctc_smem(N) <= 203 KB for every N
+                                 210 * 1024));   // one CTA per SM; ctc_smem(N) <= 205 KB for every N
     done = true;
   }
   const int64_t cap = PL_SM_COUNT;
