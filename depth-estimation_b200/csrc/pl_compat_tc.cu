@@ -350,7 +350,8 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
     }
     bar_soft();
 
-    uint32_t gch = 0, t = 0;   // A chunks produced, tiles done
+    float4 ec[RPT2], en[RPT2];   // E chunks kc and kc+1 of the running tile (carried across tiles)
+    uint32_t gch = 0, t = 0;     // A chunks produced, tiles done
     for (int64_t tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, t++) {
       const int64_t p0 = tile * kTile;
       const int rows = (int)min((int64_t)kTile, a.n - p0);
@@ -368,23 +369,22 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
 #pragma unroll
       for (int i = 0; i < RPT1; i++) mnext[i] = -INFINITY;
 
-      float4 ec[RPT2], en[RPT2], es[RPT1];
-      auto load_chunk = [&](int kc, float4* e) {
-        const float* base = a.e + s_off[kc * 8 + l2] + p0 * bw;
+      float4 es[RPT1];
+      // E chunk kc of the tile at q0 (this tile, or the next one near the end of this tile)
+      auto load_chunk = [&](int64_t q0, int qrows, int kc, float4* e) {
+        const float* base = a.e + s_off[kc * 8 + l2] + q0 * bw;
 #pragma unroll
         for (int i = 0; i < RPT2; i++) {
           const int r = g2 + i * (kSoft / 8);
-          e[i] = (r < rows && !(a.debug & 32)) ? *reinterpret_cast<const float4*>(base + r * bw)
-                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+          e[i] = (r < qrows && !(a.debug & 32)) ? *reinterpret_cast<const float4*>(base + r * bw)
+                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       };
-      load_chunk(0, ec);
+      if (t == 0) {   // the first two chunks of the CTA's first tile; later ones are requested below
+        load_chunk(p0, rows, 0, ec);
+        load_chunk(p0, rows, 1, en);
+      }
       for (int kc = 0; kc < KCH; kc++, gch++) {
-        if (kc + 1 < KCH) load_chunk(kc + 1, en);
-        // every second chunk one 64-label step of the next tile's row maxima; the loads complete
-        // under the waits and the exps below
-        const bool stat = has_next && !(kc & 1) && (kc >> 1) < SS;
-        if (stat) stat_load(np0, nrows, kc >> 1, es);
         const uint32_t ab = gch & 1;
         if (gch >= 2) TWAIT(tw0, &bar_afree[ab], ((gch >> 1) - 1) & 1);
         unsigned char* abuf = s_a + ab * kA_BUF;
@@ -411,12 +411,22 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
           *reinterpret_cast<float4*>(pa) = hi;
           *reinterpret_cast<float4*>(pa + kA_BYTES) = lo;
         }
+        if ((kc & 1) && has_next && (kc >> 1) < SS) stat_max(es, mnext);   // requested a chunk ago
+        // the proxy fence waits for this thread's outstanding loads too: the only ones in flight here
+        // are chunk kc+1's, requested a whole chunk ago
         tc::fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar_afull[ab]);
-        if ((kc & 1) && has_next && (kc >> 1) < SS) stat_max(es, mnext);   // requested a chunk ago
 #pragma unroll
         for (int i = 0; i < RPT2; i++) ec[i] = en[i];
+        // requests: E chunk kc+2 (two chunks of lookahead, maybe the next tile's) and, every second
+        // chunk, one 64-label step of the next tile's row maxima
+        if (kc + 2 < KCH) {
+          load_chunk(p0, rows, kc + 2, en);
+        } else if (has_next) {
+          load_chunk(np0, nrows, kc + 2 - KCH, en);
+        }
+        if (has_next && !(kc & 1) && (kc >> 1) < SS) stat_load(np0, nrows, kc >> 1, es);
       }
       // row sums of this tile -> epilogue warps; row maxima of the next tile -> ourselves
 #pragma unroll
