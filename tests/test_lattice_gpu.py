@@ -124,6 +124,40 @@ def test_fused_epilogue_and_strided_channels(native, oracle):
     assert _relerr(got, want[:, :7]) < TOL
 
 
+@pytest.mark.parametrize("n,d,C,scale", [
+    (3000, 5, 40, 4.0), (3000, 5, 64, 0.5), (2500, 5, 100, 12.0), (2000, 3, 48, 3.0), (2000, 2, 72, 25.0),
+    (1500, 7, 36, 2.0), (900, 10, 64, 1.0), (130, 5, 256, 2.0), (5000, 5, 68, 30.0),
+])
+def test_wide_channels_use_the_tiled_kernels(native, oracle, n, d, C, scale):
+    """C > 32 takes the tile-local splat / slice (pipelined splat for d = 5, range splat otherwise;
+    slice staging 48 / 96 / 160 rows or unstaged tiles at large feature scales; partial last channel
+    block), with and without the fused epilogue."""
+    src, ref = _rand(n, d, C, scale, seed=n + d + C)
+    lat = native.PermutohedralLattice(_cuda(ref))
+    want = oracle.filter(src, ref)
+    s = _cuda(src)
+    assert _relerr(lat.filter(s).cpu().numpy(), want) < TOL
+    assert _relerr(lat.filter(s, exact_slice=True).cpu().numpy(), want) < TOL
+    assert _relerr(lat.filter(s, flat=True).cpu().numpy(), want) < TOL
+    rng = np.random.default_rng(3)
+    add = rng.standard_normal(src.shape).astype(np.float32)
+    got = lat.filter(s, sub=s, add=_cuda(add)).cpu().numpy()
+    assert _relerr(got, add + (want - src)) < TOL
+    got = lat.filter(s, add=_cuda(add)).cpu().numpy()
+    assert _relerr(got, add + want) < TOL
+
+
+@pytest.mark.parametrize("h,w,s_ij,s_rgb,C", [(150, 200, 0.1, 0.1, 96), (150, 200, 0.01, 0.125, 64)])
+def test_image_features_wide(native, oracle, h, w, s_ij, s_rgb, C):
+    ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=5), s_ij, s_rgb)
+    src = np.random.default_rng(6).random((h * w, C)).astype(np.float32)
+    lat = native.PermutohedralLattice(_cuda(ref))
+    want = oracle.build(ref).apply(src)
+    # twice on the same handle: the second call reuses the workspace and the staging choice
+    for _ in range(2):
+        assert _relerr(lat.filter(_cuda(src)).cpu().numpy(), want) < TOL
+
+
 def test_shape_and_type_errors(native):
     ref = torch.rand(10, 3, device="cuda")
     with pytest.raises(AssertionError):
