@@ -44,6 +44,32 @@ def test_blocked_compat_tensor_core(native, L, G):
     assert N.lib().pl_debug_tc_timeouts() == 0
 
 
+@pytest.mark.parametrize("n,L", [(60001, 128), (40000, 256), (45000, 192)])
+def test_compat_many_tiles_per_cta(native, n, L):
+    """More tiles than CTAs: the double-buffered operand planes / accumulators, the next-tile row maxima
+    and the Q output rescale all wrap around several times; ragged last tile."""
+    N = native._native
+    g = torch.Generator(device="cuda").manual_seed(n + L)
+    e = torch.randn((n, L), generator=g, device="cuda") * 4
+    e[::7] += 30.0          # rows far from zero: the row maximum matters
+    e[3::11, : L // 2] -= 25.0
+    mu = (torch.from_numpy(synthetic.charb_matrix(L)) + torch.rand((L, L)) * 0.1).cuda()
+    want_q = torch.softmax(-e.double(), dim=1)
+    want_p = (want_q @ mu.double().t()) * 0.8
+    mt = mu.t().contiguous()
+    p, q = torch.full_like(e, float("nan")), torch.full_like(e, float("nan"))
+    N.check(N.lib().pl_softmax_compat(C.c_void_p(e.data_ptr()), C.c_void_p(mt.data_ptr()),
+                                      C.c_void_p(p.data_ptr()), C.c_void_p(q.data_ptr()),
+                                      n, L, 0.8, N.stream_ptr(e.device)))
+    torch.cuda.synchronize()
+    assert _rel(q, want_q) < 1e-5
+    assert _rel(p, want_p) < 1e-5
+    # per-row check as well: a wrong row sum or maximum on a few rows would hide in the global scale
+    row_err = ((p.double() - want_p).abs().amax(1) / want_p.abs().amax(1)).max()
+    assert float(row_err) < 2e-5
+    assert N.lib().pl_debug_tc_timeouts() == 0
+
+
 class _FakeGroupRun:
     """Runs LabelShardedMeanField's iteration for all ranks in lock step on one device."""
 
