@@ -19,6 +19,9 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "pl_common.cuh"
 
 namespace pl {
@@ -146,6 +149,7 @@ tile_build_kernel(const int32_t* __restrict__ vid, const float* __restrict__ bar
   if (tid == 0) {
     ustart[U] = (unsigned short)valid;
     s_off = atomicAdd(counter, U);
+    atomicMax(counter + 1, U);   // largest tile: sizes the slice kernel's staging buffer
     tile_off[tile] = s_off;
     tile_U[tile] = U;
   }
@@ -324,6 +328,7 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
   }
   if (tid == 0) {
     s_off = atomicAdd(counter, U);
+    atomicMax(counter + 1, U);   // largest tile: sizes the slice kernel's staging buffer
     tile_off[tile] = s_off;
     tile_U[tile] = U;
   }
@@ -370,22 +375,25 @@ int pow2_ceil_i(int x) {
 }  // namespace
 
 namespace {
-__global__ void max_u_kernel(const int* __restrict__ tile_U, int64_t ntiles, int* __restrict__ out);
 
 // pinned slots the devices report max U into (a ring: a stale slot can only cost speed, the
 // kernels decide staged / unstaged per tile from the tile's own U)
 int* pinned_slot() {
   static int* ring = nullptr;
-  static unsigned next = 0;
+  static std::once_flag once;
+  static std::atomic<unsigned> next{0};
   constexpr unsigned kSlots = 4096;
-  if (ring == nullptr && cudaHostAlloc((void**)&ring, kSlots * sizeof(int), cudaHostAllocPortable) != cudaSuccess)
-    return nullptr;
-  return ring + (next++ % kSlots);
+  std::call_once(once, [] {
+    if (cudaHostAlloc((void**)&ring, kSlots * sizeof(int), cudaHostAllocPortable) != cudaSuccess) {
+      (void)cudaGetLastError();
+      ring = nullptr;
+    }
+  });
+  return ring == nullptr ? nullptr : ring + (next.fetch_add(1, std::memory_order_relaxed) % kSlots);
 }
 
 int tiles_max_u(Lattice* L, cudaStream_t st) {
   int* d_max = L->tile_off + 2 * L->ntiles + 1;
-  PL_LAUNCH(max_u_kernel, grid_for((uint64_t)L->ntiles, 256, 1), 256, 0, st, L->tile_U, L->ntiles, d_max);
   L->max_U = -1;
   L->h_max_U = pinned_slot();
   if (L->h_max_U == nullptr) {
@@ -768,18 +776,6 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
     if (on0) *reinterpret_cast<float4*>(q) = a0;
     if (on1) *reinterpret_cast<float4*>(q + 32) = a1;
   }
-}
-
-// largest distinct-vertex count over the tiles (sizes the slice kernel's staging buffer)
-__global__ void __launch_bounds__(256) max_u_kernel(const int* __restrict__ tile_U, int64_t ntiles,
-                                                    int* __restrict__ out) {
-  int m = 0;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < ntiles;
-       i += (int64_t)gridDim.x * blockDim.x)
-    m = max(m, tile_U[i]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
 }
 
 }  // namespace
