@@ -181,7 +181,7 @@ class _MeanFieldLoop(torch.autograd.Function):
         with torch.cuda.device(dev):
             N.check(N.lib().pl_nchw_to_nlc(C.c_void_p(g.data_ptr()), C.c_void_p(dE_all.data_ptr()),
                                            B, L, n, 1.0, st))
-        dE0 = torch.zeros_like(dE_all)
+        dE0 = dE_all.clone()                      # sum over t of dE_t, starting with the incoming gradient
         dref = torch.zeros((B, n, d), dtype=torch.float32, device=dev) if need_ref else None
         dM = torch.zeros((L, L), dtype=torch.float32, device=dev)     # sum_t dP_t^T Q_t (unscaled)
         mu_c = mu.contiguous()
@@ -190,7 +190,6 @@ class _MeanFieldLoop(torch.autograd.Function):
             dE = dE_all[b]
             for t in range(ctx.niters - 1, -1, -1):
                 q = ctx.qs[b][t]
-                dE0[b] += dE
                 if need_ref:
                     p = torch.mm(q, mu_c.t()).mul_(s)                  # P_t, the filter's source
                     gr, wg = _grad_reference(lat, p, ctx.flat_refs[b], dE)
@@ -199,11 +198,14 @@ class _MeanFieldLoop(torch.autograd.Function):
                 else:
                     dP = lat.filter(dE, sub=dE)                        # K dE - dE
                 _xty_accumulate(dM, dP, q)
-                dQ = torch.mm(dP, mu_c).mul_(s)
-                # softmax(-E) backward: dE_prev = -Q * (dQ - sum_l dQ_l Q_l)
-                inner = (dQ * q).sum(1, keepdim=True)
-                dE = dQ.sub_(inner).mul_(q).neg_()
-            dE0[b] += dE
+                dQ = torch.mm(dP, mu_c)
+                # softmax(-E) backward with the scale, dE_prev = -s Q * (dQ - sum_l dQ_l Q_l), in place,
+                # and dE0 += dE_prev in the same pass
+                with torch.cuda.device(dev):
+                    N.check(N.lib().pl_softmax_backward(
+                        C.c_void_p(dQ.data_ptr()), C.c_void_p(q.data_ptr()), C.c_void_p(dQ.data_ptr()),
+                        C.c_void_p(dE0[b].data_ptr()), n, L, s, st))
+                dE = dQ
         grad_E0 = grad_refs = None
         if need_e0:
             grad_E0 = torch.empty((B, L, H, W), dtype=torch.float32, device=dev)

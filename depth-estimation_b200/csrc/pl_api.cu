@@ -542,6 +542,16 @@ int pl_cost_volume(const float* left_dev, const float* right_dev, float* out_dev
                          (cudaStream_t)stream);
 }
 
+int pl_softmax_backward(const float* dq_dev, const float* q_dev, float* de_dev, float* acc_dev, int64_t n,
+                        int L, float scale, void* stream) {
+  if (dq_dev == nullptr || q_dev == nullptr || de_dev == nullptr || n < 0 || L <= 0) {
+    pl::set_last_error("pl_softmax_backward: bad arguments");
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  return pl::softmax_backward(dq_dev, q_dev, de_dev, acc_dev, n, L, scale, (cudaStream_t)stream);
+}
+
 int pl_nchw_to_nlc(const float* src_dev, float* dst_dev, int64_t batch, int C, int64_t n,
                    float alpha, void* stream) {
   return pl::nchw_to_nlc(src_dev, dst_dev, batch, C, n, alpha, (cudaStream_t)stream);

@@ -125,6 +125,77 @@ transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, int row
   }
 }
 
+// Backward of Q = softmax(-E) chained with the scale of the compatibility transform, fused with the
+// accumulation of the unary gradient (crf_module.py:99-102 differentiated):
+//   dE[p][k] = -scale * q[p][k] * (dq[p][k] - sum_k' dq[p][k'] q[p][k']);   acc[p][k] += dE[p][k]
+// LPR lanes per row, float4 per lane and step.  `de` may alias `dq`.
+template <int LPR>
+__global__ void __launch_bounds__(256)
+softmax_backward_kernel(const float* dq, const float* __restrict__ q, float* de, float* acc,
+                        int64_t n, int L, float scale) {
+  constexpr int RPW = 32 / LPR;        // rows per warp
+  constexpr int MAXC = 4;              // float4 steps per lane: L <= 16 * LPR
+  const int lane = threadIdx.x & 31, l = lane % LPR;
+  const int V = L >> 2;
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t r0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW; r0 < n;
+       r0 += warps * RPW) {
+    const int64_t row = r0 + lane / LPR;
+    const bool ok = row < n;
+    float4 a[MAXC], b[MAXC];
+    float inner = 0.f;
+#pragma unroll
+    for (int c = 0; c < MAXC; c++) {
+      const int v = l + c * LPR;
+      a[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+      b[c] = a[c];
+      if (ok && v < V) {
+        a[c] = *reinterpret_cast<const float4*>(dq + row * L + 4 * v);
+        b[c] = *reinterpret_cast<const float4*>(q + row * L + 4 * v);
+      }
+      inner += a[c].x * b[c].x + a[c].y * b[c].y + a[c].z * b[c].z + a[c].w * b[c].w;
+    }
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) inner += __shfl_xor_sync(0xffffffffu, inner, o, LPR);
+#pragma unroll
+    for (int c = 0; c < MAXC; c++) {
+      const int v = l + c * LPR;
+      if (ok && v < V) {
+        float4 g;
+        g.x = -scale * b[c].x * (a[c].x - inner);
+        g.y = -scale * b[c].y * (a[c].y - inner);
+        g.z = -scale * b[c].z * (a[c].z - inner);
+        g.w = -scale * b[c].w * (a[c].w - inner);
+        *reinterpret_cast<float4*>(de + row * L + 4 * v) = g;
+        if (acc != nullptr) {
+          float4 t = *reinterpret_cast<const float4*>(acc + row * L + 4 * v);
+          t.x += g.x; t.y += g.y; t.z += g.z; t.w += g.w;
+          *reinterpret_cast<float4*>(acc + row * L + 4 * v) = t;
+        }
+      }
+    }
+  }
+}
+
+// any L / alignment: one warp per row, scalars
+__global__ void __launch_bounds__(256)
+softmax_backward_scalar_kernel(const float* dq, const float* __restrict__ q, float* de, float* acc,
+                               int64_t n, int L, float scale) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < n; row += warps) {
+    float inner = 0.f;
+    for (int k = lane; k < L; k += 32) inner += dq[row * L + k] * q[row * L + k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) inner += __shfl_xor_sync(0xffffffffu, inner, o);
+    for (int k = lane; k < L; k += 32) {
+      const float g = -scale * q[row * L + k] * (dq[row * L + k] - inner);
+      de[row * L + k] = g;
+      if (acc != nullptr) acc[row * L + k] += g;
+    }
+  }
+}
+
 }  // namespace
 
 int softmax_compat(const float* e, const float* muT, float* p, float* q_out, int64_t n, int L,
@@ -166,6 +237,29 @@ static int transpose(const float* src, float* dst, int64_t batch, int64_t rows, 
   }
   dim3 grid((unsigned)tiles, (unsigned)batch, 1);
   PL_LAUNCH(transpose_kernel, grid, 256, 0, st, src, dst, (int)rows, cols, alpha);
+  return PL_OK;
+}
+
+int softmax_backward(const float* dq, const float* q, float* de, float* acc, int64_t n, int L, float scale,
+                     cudaStream_t st) {
+  if (n == 0) return PL_OK;
+  const bool vec = (L % 4 == 0) && L <= 512 &&
+                   ((((uintptr_t)dq | (uintptr_t)q | (uintptr_t)de | (uintptr_t)acc) & 15u) == 0);
+  if (!vec) {
+    PL_LAUNCH(softmax_backward_scalar_kernel, grid_for((uint64_t)n * 32, 256, 8), 256, 0, st, dq, q, de, acc,
+              n, L, scale);
+    return PL_OK;
+  }
+  const int V = L / 4;
+  if (V <= 4) {
+    PL_LAUNCH(softmax_backward_kernel<4>, grid_for((uint64_t)n * 4, 256, 8), 256, 0, st, dq, q, de, acc, n, L, scale);
+  } else if (V <= 8) {
+    PL_LAUNCH(softmax_backward_kernel<8>, grid_for((uint64_t)n * 8, 256, 8), 256, 0, st, dq, q, de, acc, n, L, scale);
+  } else if (V <= 16) {
+    PL_LAUNCH(softmax_backward_kernel<16>, grid_for((uint64_t)n * 16, 256, 8), 256, 0, st, dq, q, de, acc, n, L, scale);
+  } else {
+    PL_LAUNCH(softmax_backward_kernel<32>, grid_for((uint64_t)n * 32, 256, 8), 256, 0, st, dq, q, de, acc, n, L, scale);
+  }
   return PL_OK;
 }
 

@@ -202,6 +202,14 @@ int pl_softargmax(const float* rows_dev, int64_t n, int L, const float* labels_d
 int pl_cost_volume(const float* left_dev, const float* right_dev, float* out_dev, int h, int w,
                    int channels, int max_disp, int window, int criterion, void* stream);
 
+/* Backward of one mean-field iteration's softmax, what autograd derives for
+ * `Q = F.softmax(-E, dim=1)` followed by the compatibility scale (crf_module.py:99-102, charb.forward :75):
+ *   de[p][k] = -scale * q[p][k] * (dq[p][k] - sum_k' dq[p][k'] q[p][k']);   acc[p][k] += de[p][k]
+ * dq_dev, q_dev, de_dev: [n][L] fp32 (de_dev may alias dq_dev); acc_dev: [n][L] running unary gradient
+ * or NULL. */
+int pl_softmax_backward(const float* dq_dev, const float* q_dev, float* de_dev, float* acc_dev, int64_t n,
+                        int L, float scale, void* stream);
+
 /* Layout helpers for the module surface (NCHW tensors <-> pixel-major):
  * dst[b][p][c] = alpha * src[b][c][p]   and back. */
 int pl_nchw_to_nlc(const float* src_dev, float* dst_dev, int64_t batch, int C, int64_t n,

@@ -48,6 +48,37 @@ def test_softmax_compat_kernel(native):
         assert _rel(p, want_p) < 1e-5
 
 
+@pytest.mark.parametrize("n,L", [(1000, 64), (777, 16), (333, 7), (130, 256), (65, 128), (50, 512), (40, 516), (9, 4)])
+def test_softmax_backward_kernel(native, n, L):
+    """pl_softmax_backward against torch autograd of scale * softmax(-E) (crf_module.py:99-102),
+    in place, with the fused accumulation of the unary gradient."""
+    import ctypes as C
+    N = native._native
+    g = torch.Generator().manual_seed(n + L)
+    e = (torch.randn((n, L), generator=g) * 2).double().requires_grad_()
+    dq = torch.randn((n, L), generator=g)
+    q = torch.softmax(-e, dim=1)
+    (q * (1.3 * dq.double())).sum().backward()
+    want = e.grad
+    acc0 = torch.randn((n, L), generator=g)
+    dq_d, q_d, acc = dq.cuda(), q.detach().float().cuda(), acc0.cuda()
+    N.check(N.lib().pl_softmax_backward(C.c_void_p(dq_d.data_ptr()), C.c_void_p(q_d.data_ptr()),
+                                        C.c_void_p(dq_d.data_ptr()), C.c_void_p(acc.data_ptr()),
+                                        n, L, 1.3, N.stream_ptr(dq_d.device)))
+    torch.cuda.synchronize()
+    assert _rel(dq_d, want) < 1e-5
+    assert _rel(acc, acc0.double() + want) < 1e-5
+    # out of place, no accumulator
+    out = torch.empty((n, L), device="cuda")
+    dq2 = dq.cuda()
+    N.check(N.lib().pl_softmax_backward(C.c_void_p(dq2.data_ptr()), C.c_void_p(q_d.data_ptr()),
+                                        C.c_void_p(out.data_ptr()), C.c_void_p(0), n, L, 1.3,
+                                        N.stream_ptr(out.device)))
+    torch.cuda.synchronize()
+    assert _rel(out, want) < 1e-5
+    assert torch.equal(dq2.cpu(), dq)
+
+
 @pytest.mark.parametrize("L", [16, 32, 64])
 def test_softmax_compat_tensor_core_path(native, L):
     """tcgen05 3xTF32 compatibility transform (pl_fused_tc.cu, MODE 2) vs fp64 and vs the
