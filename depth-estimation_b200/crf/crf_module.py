@@ -197,6 +197,14 @@ class _MeanFieldLoop(torch.autograd.Function):
                     dP = wg.sub_(dE)
                 else:
                     dP = lat.filter(dE, sub=dE)                        # K dE - dE
+                if L == 64 and dP.is_contiguous():
+                    # dQ = dP Mu, dM += dP^T Q, softmax backward and dE0 += dE in one pass (pl_backward.cu)
+                    with torch.cuda.device(dev):
+                        N.check(N.lib().pl_meanfield_backward_step(
+                            C.c_void_p(dP.data_ptr()), C.c_void_p(q.data_ptr()), C.c_void_p(mu_c.data_ptr()),
+                            C.c_void_p(dE0[b].data_ptr()), C.c_void_p(dM.data_ptr()), n, L, s, st))
+                    dE = dP
+                    continue
                 _xty_accumulate(dM, dP, q)
                 dQ = torch.mm(dP, mu_c)
                 # softmax(-E) backward with the scale, dE_prev = -s Q * (dQ - sum_l dQ_l Q_l), in place,

@@ -542,6 +542,21 @@ int pl_cost_volume(const float* left_dev, const float* right_dev, float* out_dev
                          (cudaStream_t)stream);
 }
 
+int pl_meanfield_backward_step(float* dp_dev, const float* q_dev, const float* mu_dev, float* de0_dev,
+                               float* dmu_dev, int64_t n, int L, float scale, void* stream) {
+  if (dp_dev == nullptr || q_dev == nullptr || mu_dev == nullptr || n < 0 ||
+      (((uintptr_t)dp_dev | (uintptr_t)q_dev | (uintptr_t)mu_dev | (uintptr_t)de0_dev) & 15u) != 0) {
+    pl::set_last_error("pl_meanfield_backward_step: null or misaligned pointer");
+    return PL_ERR_INVALID;
+  }
+  if (!pl::mf_backward_step_supported(L)) {
+    pl::set_last_error("pl_meanfield_backward_step: L = %d not supported (use pl_softmax_backward)", L);
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(pl::check_device());
+  return pl::mf_backward_step(dp_dev, q_dev, mu_dev, de0_dev, dmu_dev, n, L, scale, (cudaStream_t)stream);
+}
+
 int pl_softmax_backward(const float* dq_dev, const float* q_dev, float* de_dev, float* acc_dev, int64_t n,
                         int L, float scale, void* stream) {
   if (dq_dev == nullptr || q_dev == nullptr || de_dev == nullptr || n < 0 || L <= 0) {

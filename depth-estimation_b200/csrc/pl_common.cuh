@@ -158,6 +158,10 @@ int ctc_timeouts();
 // mean field (pl_meanfield.cu)
 int softmax_compat(const float* e, const float* muT, float* p, float* q_out, int64_t n, int L,
                    float scale, cudaStream_t st);
+// one backward step of the mean-field loop, L = 64 (pl_backward.cu)
+bool mf_backward_step_supported(int L);
+int mf_backward_step(float* dp, const float* q, const float* mu, float* de0, float* dmu, int64_t n,
+                     int L, float scale, cudaStream_t st);
 int softmax_backward(const float* dq, const float* q, float* de, float* acc, int64_t n, int L, float scale,
                      cudaStream_t st);
 int nchw_to_nlc(const float* src, float* dst, int64_t batch, int C, int64_t n, float alpha,

@@ -202,6 +202,15 @@ int pl_softargmax(const float* rows_dev, int64_t n, int L, const float* labels_d
 int pl_cost_volume(const float* left_dev, const float* right_dev, float* out_dev, int h, int w,
                    int channels, int max_disp, int window, int criterion, void* stream);
 
+/* One backward step of the mean-field loop in one pass (L = 64; other L: PL_ERR_INVALID, compose
+ * pl_softmax_backward with two GEMMs): what autograd derives for crf_module.py:99-102 after the filter's
+ * own backward (gaussian_matrix.py:446) has produced dP = K dE - dE:
+ *   dQ = dP Mu;   dmu += dP^T Q (unscaled, atomically);   dE = -scale Q (dQ - rowsum(dQ Q));   de0 += dE
+ * dp_dev [n][L]: dP in, dE out (in place); q_dev [n][L]: the iteration's softmax; mu_dev [L][L]: Mu[j][k]
+ * row-major; de0_dev [n][L] or NULL; dmu_dev [L][L] or NULL. */
+int pl_meanfield_backward_step(float* dp_dev, const float* q_dev, const float* mu_dev, float* de0_dev,
+                               float* dmu_dev, int64_t n, int L, float scale, void* stream);
+
 /* Backward of one mean-field iteration's softmax, what autograd derives for
  * `Q = F.softmax(-E, dim=1)` followed by the compatibility scale (crf_module.py:99-102, charb.forward :75):
  *   de[p][k] = -scale * q[p][k] * (dq[p][k] - sum_k' dq[p][k'] q[p][k']);   acc[p][k] += de[p][k]

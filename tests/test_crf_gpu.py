@@ -79,6 +79,35 @@ def test_softmax_backward_kernel(native, n, L):
     assert torch.equal(dq2.cpu(), dq)
 
 
+@pytest.mark.parametrize("n", [1, 127, 128, 1000, 40000])
+def test_meanfield_backward_step_kernel(native, n):
+    """pl_meanfield_backward_step (L = 64) against the composition it replaces, in fp64:
+    dQ = dP Mu, dMu += dP^T Q, dE = -s Q (dQ - rowsum(dQ Q)), dE0 += dE."""
+    import ctypes as C
+    N = native._native
+    L, s = 64, 0.7
+    g = torch.Generator().manual_seed(n)
+    dp = torch.randn((n, L), generator=g)
+    q = torch.softmax(torch.randn((n, L), generator=g) * 2, dim=1)
+    mu = torch.from_numpy(synthetic.charb_matrix(L)) + torch.rand((L, L), generator=g) * 0.1
+    de0 = torch.randn((n, L), generator=g)
+    dmu0 = torch.randn((L, L), generator=g)
+    dq = dp.double() @ mu.double()
+    want_de = -s * q.double() * (dq - (dq * q.double()).sum(1, keepdim=True))
+    want_dmu = dmu0.double() + dp.double().t() @ q.double()
+    dp_d, q_d, mu_d, de0_d, dmu_d = dp.cuda(), q.cuda(), mu.contiguous().cuda(), de0.cuda(), dmu0.cuda()
+    N.check(N.lib().pl_meanfield_backward_step(
+        C.c_void_p(dp_d.data_ptr()), C.c_void_p(q_d.data_ptr()), C.c_void_p(mu_d.data_ptr()),
+        C.c_void_p(de0_d.data_ptr()), C.c_void_p(dmu_d.data_ptr()), n, L, s, N.stream_ptr(dp_d.device)))
+    torch.cuda.synchronize()
+    assert _rel(dp_d, want_de) < 1e-5
+    assert _rel(de0_d, de0.double() + want_de) < 1e-5
+    assert _rel(dmu_d, want_dmu) < 1e-5
+    assert N.lib().pl_meanfield_backward_step(
+        C.c_void_p(dp_d.data_ptr()), C.c_void_p(q_d.data_ptr()), C.c_void_p(mu_d.data_ptr()),
+        C.c_void_p(0), C.c_void_p(0), n, 32, s, N.stream_ptr(dp_d.device)) != 0     # L = 64 only
+
+
 @pytest.mark.parametrize("L", [16, 32, 64])
 def test_softmax_compat_tensor_core_path(native, L):
     """tcgen05 3xTF32 compatibility transform (pl_fused_tc.cu, MODE 2) vs fp64 and vs the
