@@ -100,6 +100,20 @@ def _grad_reference(lat, src, ref, g):
     n, L = src.shape
     d = ref.shape[1]
     wg = lat.filter(g)
+    if (L % 4 == 0 and src.is_cuda and src.dtype == torch.float32 and g.dtype == torch.float32
+            and ref.dtype == torch.float32 and (lat.num_vertices + 1) * L * 4 <= (2 << 30)):
+        # the filtered outer products are only used inside inner products with the rows of src / g:
+        # per feature j, splat (g * ref_j) resp. (src * ref_j) with the factor folded into the entry
+        # weights and contract the slice with the other matrix on the spot (pl_lattice_apply_dot);
+        # neither the n x 2Ld concatenation nor its filtered copy exists
+        srcc, gc = src.contiguous(), g.contiguous()
+        t = (srcc * wg).sum(1)                       # sum_L src * W g
+        lat.filter_dot(srcc, gc, t)                  # + sum_L g * W src
+        acc = (t[:, None] * ref).contiguous()        # [n, d]
+        for j in range(d):
+            lat.filter_dot(gc, srcc, acc[:, j], rowscale=ref[:, j], coef=-1.0)
+            lat.filter_dot(srcc, gc, acc[:, j], rowscale=ref[:, j], coef=-1.0)
+        return -2 * acc, wg
     ws = lat.filter(src)
     # terms without the outer products: sum_L (src*wg + g*ws) * ref
     acc = (src * wg + g * ws).sum(1, keepdim=True) * ref  # [n, d]

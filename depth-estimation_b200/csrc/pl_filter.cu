@@ -553,6 +553,29 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
   return PL_OK;
 }
 
+int lattice_apply_dot(Lattice* L, const float* src, int64_t src_stride, int C, const float* rowscale,
+                      int64_t rs_stride, const float* other, int64_t other_stride, float* out,
+                      int64_t out_stride, float coef, cudaStream_t st) {
+  const int64_t rows = L->M + 1;
+  if (C <= 0 || C % 4 != 0 || src == nullptr || other == nullptr || out == nullptr || src_stride < C ||
+      other_stride < C || src_stride % 4 != 0 || other_stride % 4 != 0 || !aligned16(src) ||
+      !aligned16(other) || L->ntiles <= 0 || (uint64_t)rows * (uint64_t)C * sizeof(float) > (2ull << 30)) {
+    set_last_error("pl_lattice_apply_dot: unsupported arguments (C=%d)", C);
+    return PL_ERR_INVALID;
+  }
+  PL_TRY(lattice_workspace(L, C, st));
+  float* cur = L->val[0];
+  float* nxt = L->val[1];
+  const size_t row = sizeof(float) * (size_t)C;
+  PL_CUDA(cudaMemsetAsync(cur, 0, row * (size_t)rows, st));
+  PL_CUDA(cudaMemsetAsync(nxt + (size_t)L->M * C, 0, row, st));
+  PL_TRY(splat_tiled(L, src, src_stride, C, cur, st, rowscale, rs_stride));
+  float* res = nullptr;
+  PL_TRY(lattice_blur(L, cur, nxt, C, st, &res));
+  const float denom = 1 + powf(2, -L->d);  // permutohedral.h:480
+  return slice_dot_tiled(L, res, C, denom, other, other_stride, out, out_stride, coef, st);
+}
+
 int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,
                   int C, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
                   uint32_t flags, cudaStream_t st) {

@@ -490,7 +490,8 @@ constexpr int kRanges = kThreads / 8;   // 32
 
 __global__ void __launch_bounds__(kThreads, 5)
 splat_tiled_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int64_t n, int d1,
-                   const uint8_t* __restrict__ rec_splat, float* __restrict__ val) {
+                   const uint8_t* __restrict__ rec_splat, float* __restrict__ val,
+                   const float* __restrict__ rowscale, int64_t rs_stride) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* s_src = reinterpret_cast<float*>(smem_raw);                 // [kTile][kCW]
   float4* s_rec = reinterpret_cast<float4*>(s_src + kTile * kCW);    // [TE] {w, row offset, vertex, -}
@@ -507,8 +508,13 @@ splat_tiled_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, in
   for (int i = tid; i < kTile * (kCW / 4); i += kThreads) {
     const int r = i >> 4, v = i & 15;
     float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r < rows && 4 * v < cw)
+    if (r < rows && 4 * v < cw) {
       x = *reinterpret_cast<const float4*>(src + (p0 + r) * src_stride + c0 + 4 * v);
+      if (rowscale != nullptr) {   // the source is src[p][:] * rowscale[p], never materialised
+        const float sc = rowscale[(p0 + r) * rs_stride];
+        x.x *= sc; x.y *= sc; x.z *= sc; x.w *= sc;
+      }
+    }
     *reinterpret_cast<float4*>(s_src + r * kCW + 4 * v) = x;
   }
   // ... and the tile's sorted entry record (pads: weight 0 -> vertex 0, row 0)
@@ -571,7 +577,8 @@ constexpr int kRecRaw = kTEp * 9;             // bytes of a raw splat record
 
 __global__ void __launch_bounds__(kThreads, 2)
 splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int64_t n, int nblk,
-                  int64_t nitems, const uint8_t* __restrict__ rec_splat, float* __restrict__ val) {
+                  int64_t nitems, const uint8_t* __restrict__ rec_splat, float* __restrict__ val,
+                  const float* __restrict__ rowscale, int64_t rs_stride) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* s_src = reinterpret_cast<float*>(smem_raw);                    // [2][kTile][kCW]
   unsigned char* s_raw = smem_raw + 2 * kTile * kCW * sizeof(float);    // [2][kRecRaw]
@@ -635,6 +642,9 @@ splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int
       const int k = rg * kERp + j * 8 + l;
       w[j] = rw[k];
       key[j] = (rv[k] << 7) | (int)rp[k];
+      // optional per-row factor of the source (src[p][:] * rowscale[p]) folded into the entry weight;
+      // pads carry weight 0 and row 0 of the tile, which always exists
+      if (rowscale != nullptr) w[j] *= rowscale[(tile * kTile + (int64_t)rp[k]) * rs_stride];
     }
     const float* sb = s_src + sbuf * (kTile * kCW) + 4 * l;
     float* vbase = val + c0 + 4 * l;
@@ -778,11 +788,102 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
   }
 }
 
+// ---------------------------------------------------------------------------
+// slice contracted on the spot: out[p] += coef * sum_c slice(val)[p][c] * other[p][c].
+// The guide gradient (gaussian_matrix.py:450-463) needs the filtered outer products only
+// inside such inner products with src / grad rows, so the n x C filter output never exists.
+// Same layout as slice_tiled_kernel; the 8 lanes of a row combine with shuffles, channel blocks
+// (grid.y) with one atomic per row.
+// ---------------------------------------------------------------------------
+template <int STAGE>
+__global__ void __launch_bounds__(kThreads, 4)
+slice_dot_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
+                 const uint8_t* __restrict__ rec_slice, const int32_t* __restrict__ vid,
+                 const int2* __restrict__ useg, const int* __restrict__ tile_off,
+                 const int* __restrict__ tile_U, float denom, const float* __restrict__ other,
+                 int64_t other_stride, float* out, int64_t out_stride, float coef) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* s_val = reinterpret_cast<float*>(smem_raw);                         // [STAGE][kCW]
+  float2* s_ent = reinterpret_cast<float2*>(s_val + STAGE * kCW);            // [TE] {weight, row}
+
+  const int tid = threadIdx.x;
+  const int64_t tile = blockIdx.x;
+  const int c0 = blockIdx.y * kCW;
+  const int cw = min(kCW, Cc - c0);
+  const int TE = kTile * d1;
+  const int64_t p0 = tile * kTile;
+  const int rows = (int)min((int64_t)kTile, n - p0);
+  const int U = tile_U[tile];
+  const bool staged = U <= STAGE;
+  const float inv = coef / denom;
+
+  if (staged) {
+    const int2* seg = useg + tile_off[tile];
+    for (int i = tid; i < U * 16; i += kThreads) {
+      const int u = i >> 4, v = i & 15;
+      if (4 * v < cw)
+        *reinterpret_cast<float4*>(s_val + u * kCW + 4 * v) =
+            *reinterpret_cast<const float4*>(val + (int64_t)seg[u].x * Cc + c0 + 4 * v);
+    }
+  }
+  const float* rs_bary = reinterpret_cast<const float*>(rec_slice + tile * (int64_t)TE * 6);
+  const uint16_t* rs_loc = reinterpret_cast<const uint16_t*>(rs_bary + TE);
+  const int valid = rows * d1;
+  for (int i = tid; i < TE; i += kThreads) {
+    int ix = 0;
+    if (i < valid) ix = staged ? (int)rs_loc[i] * kCW : vid[tile * TE + i];
+    s_ent[i] = make_float2(rs_bary[i], __int_as_float(ix));
+  }
+  __syncthreads();
+
+  const int g = tid >> 3, l = tid & 7;
+  const bool on0 = 4 * l < cw, on1 = 32 + 4 * l < cw;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+  for (int r0 = 0; r0 < kTile; r0 += kThreads / 8) {   // whole warps stay in the loop for the shuffles
+    const int r = r0 + g;
+    const bool ok = r < rows;
+    const int64_t p = p0 + (ok ? r : 0);
+    float4 o0 = zero, o1 = zero;
+    if (ok) {
+      const float* q = other + p * other_stride + c0 + 4 * l;
+      if (on0) o0 = *reinterpret_cast<const float4*>(q);
+      if (on1) o1 = *reinterpret_cast<const float4*>(q + 32);
+    }
+    float4 a0 = zero, a1 = zero;
+    if (ok) {
+      for (int j = 0; j < d1; j++) {
+        const float2 e = s_ent[r * d1 + j];
+        const int ix = __float_as_int(e.y);
+        float4 x0 = zero, x1 = zero;
+        if (staged) {
+          if (on0) x0 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l);
+          if (on1) x1 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l + 32);
+        } else {
+          const float* q = val + (int64_t)ix * Cc + c0 + 4 * l;
+          if (on0) x0 = *reinterpret_cast<const float4*>(q);
+          if (on1) x1 = *reinterpret_cast<const float4*>(q + 32);
+        }
+        fma4(a0, e.x, x0);
+        fma4(a1, e.x, x1);
+      }
+    }
+    float dot = a0.x * o0.x + a0.y * o0.y + a0.z * o0.z + a0.w * o0.w +
+                a1.x * o1.x + a1.y * o1.y + a1.z * o1.z + a1.w * o1.w;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o, 8);
+    if (ok && l == 0) {
+      if (gridDim.y == 1) out[p * out_stride] += inv * dot;
+      else atomicAdd(out + p * out_stride, inv * dot);
+    }
+  }
+}
+
 }  // namespace
 
 // val must be zeroed by the caller.  Requires Cc % 4 == 0 and 16-byte aligned rows.
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
-                cudaStream_t st) {
+                cudaStream_t st, const float* rowscale, int64_t rs_stride) {
   const int d1 = L->d + 1;
   const size_t smem = sizeof(float) * kTile * kCW + sizeof(float4) * (size_t)kTile * d1;
   static bool attr_done = false;
@@ -800,12 +901,12 @@ int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float*
     const size_t smem_p = 2 * sizeof(float) * kTile * kCW + 2 * (size_t)kRecRaw;
     const int64_t cap = 2 * PL_SM_COUNT;
     PL_LAUNCH(splat_pipe_kernel, (unsigned)(nitems < cap ? nitems : cap), kThreads, smem_p, st, src,
-              src_stride, Cc, L->n, nblk, nitems, L->rec_splat, val);
+              src_stride, Cc, L->n, nblk, nitems, L->rec_splat, val, rowscale, rs_stride);
     return PL_OK;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
   PL_LAUNCH(splat_tiled_kernel, grid, kThreads, smem, st, src, src_stride, Cc, L->n, d1,
-            L->rec_splat, val);
+            L->rec_splat, val, rowscale, rs_stride);
   return PL_OK;
 }
 
@@ -852,6 +953,38 @@ int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, i
   if (L->max_U <= 96) PL_SLICE(false, 96);
   PL_SLICE(false, 160);
 #undef PL_SLICE
+}
+
+int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const float* other,
+                    int64_t other_stride, float* out, int64_t out_stride, float coef, cudaStream_t st) {
+  if (L->max_U < 0) {
+    PL_CUDA(cudaEventSynchronize(L->max_U_ev));
+    L->max_U = *L->h_max_U;
+  }
+  const int d1 = L->d + 1;
+  static bool attr_done = false;
+  if (!attr_done) {
+    PL_CUDA(cudaFuncSetAttribute(slice_dot_kernel<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    PL_CUDA(cudaFuncSetAttribute(slice_dot_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    PL_CUDA(cudaFuncSetAttribute(slice_dot_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    attr_done = true;
+  }
+  dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
+  const size_t ent = sizeof(float2) * (size_t)kTile * d1;
+  if (L->max_U <= 48) {
+    PL_LAUNCH(slice_dot_kernel<48>, grid, kThreads, sizeof(float) * 48 * kCW + ent, st, val, Cc, L->n, d1,
+              L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, other, other_stride, out,
+              out_stride, coef);
+  } else if (L->max_U <= 96) {
+    PL_LAUNCH(slice_dot_kernel<96>, grid, kThreads, sizeof(float) * 96 * kCW + ent, st, val, Cc, L->n, d1,
+              L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, other, other_stride, out,
+              out_stride, coef);
+  } else {
+    PL_LAUNCH(slice_dot_kernel<160>, grid, kThreads, sizeof(float) * 160 * kCW + ent, st, val, Cc, L->n, d1,
+              L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, other, other_stride, out,
+              out_stride, coef);
+  }
+  return PL_OK;
 }
 
 }  // namespace pl

@@ -98,6 +98,29 @@ class PermutohedralLattice:
 
     __call__ = filter
 
+    def filter_dot(self, src, other, out, rowscale=None, coef=1.0):
+        """``out[p] += coef * <filter(src * rowscale[:, None])[p], other[p]>`` without materialising
+        the scaled source or the filtered rows (the guide gradient, gaussian_matrix.py:450-463).
+        ``out`` and ``rowscale`` are 1-D views with any stride (columns of [n, d] matrices)."""
+        self._check_rows(src, "src")
+        self._check_rows(other, "other")
+        src, other = _rowmajor(src), _rowmajor(other)
+        c = int(src.shape[1])
+        if other.shape[1] != c or out.shape[0] != self.n or out.dim() != 1:
+            raise ValueError("filter_dot: other must be [n, C] and out [n]")
+        rs_ptr, rs_stride = C.c_void_p(0), 0
+        if rowscale is not None:
+            if rowscale.dim() != 1 or rowscale.shape[0] != self.n or rowscale.dtype != torch.float32:
+                raise ValueError("filter_dot: rowscale must be float32 [n]")
+            rs_ptr, rs_stride = C.c_void_p(rowscale.data_ptr()), rowscale.stride(0)
+        with torch.cuda.device(self.device):
+            N.check(N.lib().pl_lattice_apply_dot(
+                self._h, C.c_void_p(src.data_ptr()), src.stride(0), c, rs_ptr, rs_stride,
+                C.c_void_p(other.data_ptr()), other.stride(0), C.c_void_p(out.data_ptr()), out.stride(0),
+                float(coef), N.stream_ptr(self.device)))
+        return out
+
+
     def mean_field(self, e0, mu, niters, scale=1.0, exact_slice=False, flat=False, unfused=False,
                    no_tensor=False, tile_kernel=False):
         """Pixel-major CRFasRNN inference loop (crf_module.py:97-103).

@@ -111,6 +111,16 @@ int pl_lattice_apply(pl_lattice* lat, const float* src_dev, int64_t src_stride, 
                      int64_t dst_stride, int C, const float* sub_dev, int64_t sub_stride,
                      const float* add_dev, int64_t add_stride, uint32_t flags, void* stream);
 
+/* The filter contracted on the spot, for the guide gradient of LatticeFilter.backward
+ * (crf/gaussian_matrix.py:450-463), whose filtered outer products `filter(g (x) ref)` are only ever
+ * used inside inner products with the rows of src / g:
+ *   out[p * out_stride] += coef * sum_c filter(x)[p][c] * other[p][c],   x[p][c] = src[p][c] * rowscale[p * rowscale_stride]
+ * (rowscale_dev NULL: x = src).  Neither x nor filter(x) is written to memory.  C % 4 == 0, 16-byte aligned
+ * rows, lattice built with its tile view (the default); otherwise PL_ERR_INVALID. */
+int pl_lattice_apply_dot(pl_lattice* lat, const float* src_dev, int64_t src_stride, int C,
+                         const float* rowscale_dev, int64_t rowscale_stride, const float* other_dev,
+                         int64_t other_stride, float* out_dev, int64_t out_stride, float coef, void* stream);
+
 /* ---- the reference's call shape ------------------------------------------- */
 
 /* lattice.cpp:6-10  filter(src[n,C], ref[n,d]) -> dst[n,C], device buffers. */

@@ -158,6 +158,50 @@ def test_image_features_wide(native, oracle, h, w, s_ij, s_rgb, C):
         assert _relerr(lat.filter(_cuda(src)).cpu().numpy(), want) < TOL
 
 
+@pytest.mark.parametrize("n,d,C,scale", [
+    (3000, 5, 64, 4.0), (2500, 5, 100, 12.0), (777, 5, 8, 2.0), (2000, 3, 48, 3.0), (1500, 7, 36, 30.0),
+    (130, 5, 256, 2.0), (4100, 5, 4, 6.0),
+])
+def test_filter_dot_matches_composition(native, oracle, n, d, C, scale):
+    """pl_lattice_apply_dot: out += coef * <filter(src * rowscale), other> against the oracle filter of the
+    materialised product (the contraction the guide gradient needs, gaussian_matrix.py:450-463)."""
+    src, ref = _rand(n, d, C, scale, seed=n + C)
+    rng = np.random.default_rng(11)
+    other = rng.standard_normal((n, C)).astype(np.float32)
+    rs = rng.standard_normal((n, d)).astype(np.float32)
+    out0 = rng.standard_normal((n, d)).astype(np.float32)
+    lat = native.PermutohedralLattice(_cuda(ref))
+    out = _cuda(out0)
+    rsd = _cuda(rs)
+    for j in (0, d - 1):
+        lat.filter_dot(_cuda(src), _cuda(other), out[:, j], rowscale=rsd[:, j], coef=-0.5)
+    lat.filter_dot(_cuda(src), _cuda(other), out[:, 0], coef=2.0)          # no row factor
+    want = out0.astype(np.float64).copy()
+    for j in (0, d - 1):
+        f = oracle.filter(src * rs[:, j:j + 1], ref).astype(np.float64)
+        want[:, j] += -0.5 * (f * other).sum(1)
+    want[:, 0] += 2.0 * (oracle.filter(src, ref).astype(np.float64) * other).sum(1)
+    assert _relerr(out.cpu().numpy(), want) < TOL
+
+
+def test_guide_gradient_contracted_path_matches_slab_path(native):
+    """_grad_reference with the contracted filter (L % 4 == 0) against its own slab form (the reference's
+    arithmetic per column, checked against the golden gradients elsewhere)."""
+    gm = importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
+    ref = torch.from_numpy(synthetic.ijrgb_features(synthetic.image(60, 80, seed=3))).cuda()
+    g = torch.Generator(device="cuda").manual_seed(5)
+    src = torch.rand((ref.shape[0], 16), generator=g, device="cuda")
+    grad = torch.randn((ref.shape[0], 16), generator=g, device="cuda")
+    lat = native.PermutohedralLattice(ref)
+    fast, wg_fast = gm._grad_reference(lat, src, ref, grad)
+    # 15 channels + a zero column: same sums, but L % 4 != 0 never takes the contracted path
+    slow, wg_slow = gm._grad_reference(lat, src[:, :15].contiguous(), ref, grad[:, :15].contiguous())
+    fast15, _ = gm._grad_reference(lat, torch.cat([src[:, :15], torch.zeros_like(src[:, :1])], 1).contiguous(), ref,
+                                   torch.cat([grad[:, :15], torch.zeros_like(src[:, :1])], 1).contiguous())
+    assert _relerr(fast15.cpu().numpy(), slow.cpu().numpy()) < 2e-4
+    assert fast.shape == slow.shape and torch.isfinite(fast).all()
+
+
 def test_shape_and_type_errors(native):
     ref = torch.rand(10, 3, device="cuda")
     with pytest.raises(AssertionError):
