@@ -67,6 +67,9 @@ _SIGNATURES = {
                                  C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "pl_lattice_apply_dot": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64,
                                        C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]),
+    "pl_lattice_apply_dot_multi": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64,
+                                             C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_float,
+                                             C.c_void_p]),
     "pl_meanfield_backward_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_int64, C.c_int, C.c_float, C.c_void_p]),
     "pl_softmax_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int,

@@ -110,6 +110,12 @@ def _grad_reference(lat, src, ref, g):
         t = (srcc * wg).sum(1)                       # sum_L src * W g
         lat.filter_dot(srcc, gc, t)                  # + sum_L g * W src
         acc = (t[:, None] * ref).contiguous()        # [n, d]
+        if d == 5 and ref.stride(1) == 1 and lat.num_vertices < (1 << 24):
+            # all five features in one pass per side: source rows staged once for the five scaled
+            # splats, rows of the other matrix read once for the five contractions
+            lat.filter_dot_multi(gc, srcc, acc, ref, coef=-1.0)
+            lat.filter_dot_multi(srcc, gc, acc, ref, coef=-1.0)
+            return -2 * acc, wg
         for j in range(d):
             lat.filter_dot(gc, srcc, acc[:, j], rowscale=ref[:, j], coef=-1.0)
             lat.filter_dot(srcc, gc, acc[:, j], rowscale=ref[:, j], coef=-1.0)

@@ -241,6 +241,16 @@ int pl_lattice_apply_dot(pl_lattice* lat, const float* src_dev, int64_t src_stri
                                (cudaStream_t)stream);
 }
 
+int pl_lattice_apply_dot_multi(pl_lattice* lat, const float* src_dev, int64_t src_stride, int C,
+                               const float* rowscale_dev, int64_t rowscale_stride, int J,
+                               const float* other_dev, int64_t other_stride, float* out_dev,
+                               int64_t out_stride, float coef, void* stream) {
+  if (lat == nullptr) return PL_ERR_INVALID;
+  return pl::lattice_apply_dot(reinterpret_cast<Lattice*>(lat), src_dev, src_stride, C, rowscale_dev,
+                               rowscale_stride, other_dev, other_stride, out_dev, out_stride, coef,
+                               (cudaStream_t)stream, J);
+}
+
 int pl_filter(const float* src_dev, const float* ref_dev, float* dst_dev, int64_t n, int C, int d,
               void* stream) {
   pl_lattice* lat = nullptr;

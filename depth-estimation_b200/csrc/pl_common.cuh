@@ -108,13 +108,15 @@ int lattice_build(Lattice* L, const float* ref, cudaStream_t st, const GuideSrc*
 // tile-local view + tiled kernels (pl_tiles.cu)
 int lattice_build_tiles(Lattice* L, cudaStream_t st);
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
-                cudaStream_t st, const float* rowscale = nullptr, int64_t rs_stride = 0);
+                cudaStream_t st, const float* rowscale = nullptr, int64_t rs_stride = 0, int J = 1);
 int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const float* other,
-                    int64_t other_stride, float* out, int64_t out_stride, float coef, cudaStream_t st);
+                    int64_t other_stride, float* out, int64_t out_stride, float coef, cudaStream_t st,
+                    int J = 1);
 // out[p] += coef * <filter(src * rowscale)[p][:], other[p][:]>  (pl_filter.cu; tiled kernels only)
+// J > 1: J row factors rowscale[p][j] at once, out[p][j] (d = 5, J = 5 only)
 int lattice_apply_dot(Lattice* L, const float* src, int64_t src_stride, int C, const float* rowscale,
                       int64_t rs_stride, const float* other, int64_t other_stride, float* out,
-                      int64_t out_stride, float coef, cudaStream_t st);
+                      int64_t out_stride, float coef, cudaStream_t st, int J = 1);
 int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, int64_t dst_stride,
                 const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
                 bool exact, cudaStream_t st);

@@ -555,10 +555,16 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
 
 int lattice_apply_dot(Lattice* L, const float* src, int64_t src_stride, int C, const float* rowscale,
                       int64_t rs_stride, const float* other, int64_t other_stride, float* out,
-                      int64_t out_stride, float coef, cudaStream_t st) {
+                      int64_t out_stride, float coef, cudaStream_t st, int J) {
   const int64_t rows = L->M + 1;
-  if (C <= 0 || C % 4 != 0 || src == nullptr || other == nullptr || out == nullptr || src_stride < C ||
-      other_stride < C || src_stride % 4 != 0 || other_stride % 4 != 0 || !aligned16(src) ||
+  if (J < 1 || (J > 1 && (J != 5 || L->d != 5 || rowscale == nullptr || L->M >= (1 << 24)))) {
+    set_last_error("pl_lattice_apply_dot: %d row factors at once is not supported here", J);
+    return PL_ERR_INVALID;
+  }
+  const int Cs = C;   // channels of the source; the value rows carry J * C
+  C = J * Cs;
+  if (Cs <= 0 || Cs % 4 != 0 || src == nullptr || other == nullptr || out == nullptr || src_stride < Cs ||
+      other_stride < Cs || src_stride % 4 != 0 || other_stride % 4 != 0 || !aligned16(src) ||
       !aligned16(other) || L->ntiles <= 0 || (uint64_t)rows * (uint64_t)C * sizeof(float) > (2ull << 30)) {
     set_last_error("pl_lattice_apply_dot: unsupported arguments (C=%d)", C);
     return PL_ERR_INVALID;
@@ -569,11 +575,11 @@ int lattice_apply_dot(Lattice* L, const float* src, int64_t src_stride, int C, c
   const size_t row = sizeof(float) * (size_t)C;
   PL_CUDA(cudaMemsetAsync(cur, 0, row * (size_t)rows, st));
   PL_CUDA(cudaMemsetAsync(nxt + (size_t)L->M * C, 0, row, st));
-  PL_TRY(splat_tiled(L, src, src_stride, C, cur, st, rowscale, rs_stride));
+  PL_TRY(splat_tiled(L, src, src_stride, Cs, cur, st, rowscale, rs_stride, J));
   float* res = nullptr;
   PL_TRY(lattice_blur(L, cur, nxt, C, st, &res));
   const float denom = 1 + powf(2, -L->d);  // permutohedral.h:480
-  return slice_dot_tiled(L, res, C, denom, other, other_stride, out, out_stride, coef, st);
+  return slice_dot_tiled(L, res, Cs, denom, other, other_stride, out, out_stride, coef, st, J);
 }
 
 int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,

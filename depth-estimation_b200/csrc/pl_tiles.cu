@@ -575,6 +575,9 @@ constexpr int kTEp = kTile * kD1p;            // 768 entries
 constexpr int kERp = kTEp / kRanges;          // 24 entries per range
 constexpr int kRecRaw = kTEp * 9;             // bytes of a raw splat record
 
+// J > 1: J sources at once, src[p][:] * rowscale[p][j] for j < J, into value rows of J * Cc channels
+// ([j][c]): the src tile is staged and gathered once for all of them, only the weights differ.
+template <int J>
 __global__ void __launch_bounds__(kThreads, 2)
 splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int64_t n, int nblk,
                   int64_t nitems, const uint8_t* __restrict__ rec_splat, float* __restrict__ val,
@@ -644,12 +647,16 @@ splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int
       key[j] = (rv[k] << 7) | (int)rp[k];
       // optional per-row factor of the source (src[p][:] * rowscale[p]) folded into the entry weight;
       // pads carry weight 0 and row 0 of the tile, which always exists
-      if (rowscale != nullptr) w[j] *= rowscale[(tile * kTile + (int64_t)rp[k]) * rs_stride];
+      if (J == 1 && rowscale != nullptr) w[j] *= rowscale[(tile * kTile + (int64_t)rp[k]) * rs_stride];
     }
     const float* sb = s_src + sbuf * (kTile * kCW) + 4 * l;
+    const int64_t Cv = (int64_t)J * Cc;            // channels of a value row
     float* vbase = val + c0 + 4 * l;
+    const float* rs_tile = (J > 1) ? rowscale + tile * kTile * rs_stride : nullptr;
     int cur = -1;
-    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    float4 a0[J], a1[J];
+#pragma unroll
+    for (int q = 0; q < J; q++) a0[q] = a1[q] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int j = 0; j < 3; j++) {
 #pragma unroll
@@ -659,20 +666,39 @@ splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int
         const int v = kk >> 7;
         if (v != cur) {
           if (cur >= 0) {
-            if (on0) red_add_v4(vbase + (int64_t)cur * Cc, a0);
-            if (on1) red_add_v4(vbase + (int64_t)cur * Cc + 32, a1);
+#pragma unroll
+            for (int q = 0; q < J; q++) {
+              if (on0) red_add_v4(vbase + (int64_t)cur * Cv + q * Cc, a0[q]);
+              if (on1) red_add_v4(vbase + (int64_t)cur * Cv + q * Cc + 32, a1[q]);
+            }
           }
           cur = v;
-          a0 = make_float4(0.f, 0.f, 0.f, 0.f);
-          a1 = a0;
+#pragma unroll
+          for (int q = 0; q < J; q++) a0[q] = a1[q] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        const float* row = sb + (kk & 127) * kCW;
-        fma4(a0, wk, *reinterpret_cast<const float4*>(row));
-        fma4(a1, wk, *reinterpret_cast<const float4*>(row + 32));
+        const int pix = kk & 127;
+        const float* row = sb + pix * kCW;
+        const float4 x0 = *reinterpret_cast<const float4*>(row);
+        const float4 x1 = *reinterpret_cast<const float4*>(row + 32);
+        if (J == 1) {
+          fma4(a0[0], wk, x0);
+          fma4(a1[0], wk, x1);
+        } else {
+          const float* rsp = rs_tile + (int64_t)pix * rs_stride;   // L1-resident: 128 x J floats per tile
+#pragma unroll
+          for (int q = 0; q < J; q++) {
+            const float wq = wk * rsp[q];
+            fma4(a0[q], wq, x0);
+            fma4(a1[q], wq, x1);
+          }
+        }
       }
     }
-    if (on0) red_add_v4(vbase + (int64_t)cur * Cc, a0);
-    if (on1) red_add_v4(vbase + (int64_t)cur * Cc + 32, a1);
+#pragma unroll
+    for (int q = 0; q < J; q++) {
+      if (on0) red_add_v4(vbase + (int64_t)cur * Cv + q * Cc, a0[q]);
+      if (on1) red_add_v4(vbase + (int64_t)cur * Cv + q * Cc + 32, a1[q]);
+    }
   }
 }
 
@@ -796,12 +822,12 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
 // (grid.y) with one atomic per row.
 // ---------------------------------------------------------------------------
 template <int STAGE>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 3)
 slice_dot_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
                  const uint8_t* __restrict__ rec_slice, const int32_t* __restrict__ vid,
                  const int2* __restrict__ useg, const int* __restrict__ tile_off,
                  const int* __restrict__ tile_U, float denom, const float* __restrict__ other,
-                 int64_t other_stride, float* out, int64_t out_stride, float coef) {
+                 int64_t other_stride, float* out, int64_t out_stride, float coef, int J) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* s_val = reinterpret_cast<float*>(smem_raw);                         // [STAGE][kCW]
   float2* s_ent = reinterpret_cast<float2*>(s_val + STAGE * kCW);            // [TE] {weight, row}
@@ -817,15 +843,6 @@ slice_dot_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
   const bool staged = U <= STAGE;
   const float inv = coef / denom;
 
-  if (staged) {
-    const int2* seg = useg + tile_off[tile];
-    for (int i = tid; i < U * 16; i += kThreads) {
-      const int u = i >> 4, v = i & 15;
-      if (4 * v < cw)
-        *reinterpret_cast<float4*>(s_val + u * kCW + 4 * v) =
-            *reinterpret_cast<const float4*>(val + (int64_t)seg[u].x * Cc + c0 + 4 * v);
-    }
-  }
   const float* rs_bary = reinterpret_cast<const float*>(rec_slice + tile * (int64_t)TE * 6);
   const uint16_t* rs_loc = reinterpret_cast<const uint16_t*>(rs_bary + TE);
   const int valid = rows * d1;
@@ -834,47 +851,66 @@ slice_dot_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
     if (i < valid) ix = staged ? (int)rs_loc[i] * kCW : vid[tile * TE + i];
     s_ent[i] = make_float2(rs_bary[i], __int_as_float(ix));
   }
-  __syncthreads();
-
   const int g = tid >> 3, l = tid & 7;
   const bool on0 = 4 * l < cw, on1 = 32 + 4 * l < cw;
   const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 2
-  for (int r0 = 0; r0 < kTile; r0 += kThreads / 8) {   // whole warps stay in the loop for the shuffles
-    const int r = r0 + g;
-    const bool ok = r < rows;
-    const int64_t p = p0 + (ok ? r : 0);
-    float4 o0 = zero, o1 = zero;
-    if (ok) {
-      const float* q = other + p * other_stride + c0 + 4 * l;
-      if (on0) o0 = *reinterpret_cast<const float4*>(q);
-      if (on1) o1 = *reinterpret_cast<const float4*>(q + 32);
+  const int64_t Cv = (int64_t)J * Cc;     // channels of a value row: [j][c]
+  // the rows of `other` this thread contracts with, once for all J blocks
+  float4 o0[kTile * 8 / kThreads], o1[kTile * 8 / kThreads];
+#pragma unroll
+  for (int i = 0; i < kTile * 8 / kThreads; i++) {
+    const int r = g + i * (kThreads / 8);
+    o0[i] = o1[i] = zero;
+    if (r < rows) {
+      const float* q = other + (p0 + r) * other_stride + c0 + 4 * l;
+      if (on0) o0[i] = *reinterpret_cast<const float4*>(q);
+      if (on1) o1[i] = *reinterpret_cast<const float4*>(q + 32);
     }
-    float4 a0 = zero, a1 = zero;
-    if (ok) {
-      for (int j = 0; j < d1; j++) {
-        const float2 e = s_ent[r * d1 + j];
-        const int ix = __float_as_int(e.y);
-        float4 x0 = zero, x1 = zero;
-        if (staged) {
-          if (on0) x0 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l);
-          if (on1) x1 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l + 32);
-        } else {
-          const float* q = val + (int64_t)ix * Cc + c0 + 4 * l;
-          if (on0) x0 = *reinterpret_cast<const float4*>(q);
-          if (on1) x1 = *reinterpret_cast<const float4*>(q + 32);
-        }
-        fma4(a0, e.x, x0);
-        fma4(a1, e.x, x1);
+  }
+  for (int jb = 0; jb < J; jb++) {
+    const float* vj = val + (int64_t)jb * Cc + c0;
+    __syncthreads();   // the previous block's staged rows are dead (and s_ent is written)
+    if (staged) {
+      const int2* seg = useg + tile_off[tile];
+      for (int i = tid; i < U * 16; i += kThreads) {
+        const int u = i >> 4, v = i & 15;
+        if (4 * v < cw)
+          *reinterpret_cast<float4*>(s_val + u * kCW + 4 * v) =
+              *reinterpret_cast<const float4*>(vj + (int64_t)seg[u].x * Cv + 4 * v);
       }
     }
-    float dot = a0.x * o0.x + a0.y * o0.y + a0.z * o0.z + a0.w * o0.w +
-                a1.x * o1.x + a1.y * o1.y + a1.z * o1.z + a1.w * o1.w;
+    __syncthreads();
 #pragma unroll
-    for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o, 8);
-    if (ok && l == 0) {
-      if (gridDim.y == 1) out[p * out_stride] += inv * dot;
-      else atomicAdd(out + p * out_stride, inv * dot);
+    for (int i = 0; i < kTile * 8 / kThreads; i++) {   // whole warps stay in the loop for the shuffles
+      const int r = g + i * (kThreads / 8);
+      const bool ok = r < rows;
+      float4 a0 = zero, a1 = zero;
+      if (ok) {
+        for (int j = 0; j < d1; j++) {
+          const float2 e = s_ent[r * d1 + j];
+          const int ix = __float_as_int(e.y);
+          float4 x0 = zero, x1 = zero;
+          if (staged) {
+            if (on0) x0 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l);
+            if (on1) x1 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l + 32);
+          } else {
+            const float* q = vj + (int64_t)ix * Cv + 4 * l;
+            if (on0) x0 = *reinterpret_cast<const float4*>(q);
+            if (on1) x1 = *reinterpret_cast<const float4*>(q + 32);
+          }
+          fma4(a0, e.x, x0);
+          fma4(a1, e.x, x1);
+        }
+      }
+      float dot = a0.x * o0[i].x + a0.y * o0[i].y + a0.z * o0[i].z + a0.w * o0[i].w +
+                  a1.x * o1[i].x + a1.y * o1[i].y + a1.z * o1[i].z + a1.w * o1[i].w;
+#pragma unroll
+      for (int o = 4; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o, 8);
+      if (ok && l == 0) {
+        float* dst = out + (p0 + r) * out_stride + jb;
+        if (gridDim.y == 1) *dst += inv * dot;
+        else atomicAdd(dst, inv * dot);
+      }
     }
   }
 }
@@ -883,14 +919,16 @@ slice_dot_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
 
 // val must be zeroed by the caller.  Requires Cc % 4 == 0 and 16-byte aligned rows.
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
-                cudaStream_t st, const float* rowscale, int64_t rs_stride) {
+                cudaStream_t st, const float* rowscale, int64_t rs_stride, int J) {
   const int d1 = L->d + 1;
   const size_t smem = sizeof(float) * kTile * kCW + sizeof(float4) * (size_t)kTile * d1;
   static bool attr_done = false;
   if (!attr_done) {
     PL_CUDA(cudaFuncSetAttribute(splat_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  100 * 1024));
-    PL_CUDA(cudaFuncSetAttribute(splat_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PL_CUDA(cudaFuncSetAttribute(splat_pipe_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 100 * 1024));
+    PL_CUDA(cudaFuncSetAttribute(splat_pipe_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  100 * 1024));
     attr_done = true;
   }
@@ -900,9 +938,20 @@ int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float*
     const int64_t nitems = L->ntiles * nblk;
     const size_t smem_p = 2 * sizeof(float) * kTile * kCW + 2 * (size_t)kRecRaw;
     const int64_t cap = 2 * PL_SM_COUNT;
-    PL_LAUNCH(splat_pipe_kernel, (unsigned)(nitems < cap ? nitems : cap), kThreads, smem_p, st, src,
-              src_stride, Cc, L->n, nblk, nitems, L->rec_splat, val, rowscale, rs_stride);
-    return PL_OK;
+    if (J == 5) {
+      PL_LAUNCH(splat_pipe_kernel<5>, (unsigned)(nitems < cap ? nitems : cap), kThreads, smem_p, st, src,
+                src_stride, Cc, L->n, nblk, nitems, L->rec_splat, val, rowscale, rs_stride);
+      return PL_OK;
+    }
+    if (J == 1) {
+      PL_LAUNCH(splat_pipe_kernel<1>, (unsigned)(nitems < cap ? nitems : cap), kThreads, smem_p, st, src,
+                src_stride, Cc, L->n, nblk, nitems, L->rec_splat, val, rowscale, rs_stride);
+      return PL_OK;
+    }
+  }
+  if (J != 1) {
+    set_last_error("splat_tiled: %d row factors at once needs d = 5 and J = 5", J);
+    return PL_ERR_INVALID;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
   PL_LAUNCH(splat_tiled_kernel, grid, kThreads, smem, st, src, src_stride, Cc, L->n, d1,
@@ -956,7 +1005,8 @@ int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, i
 }
 
 int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const float* other,
-                    int64_t other_stride, float* out, int64_t out_stride, float coef, cudaStream_t st) {
+                    int64_t other_stride, float* out, int64_t out_stride, float coef, cudaStream_t st,
+                    int J) {
   if (L->max_U < 0) {
     PL_CUDA(cudaEventSynchronize(L->max_U_ev));
     L->max_U = *L->h_max_U;
@@ -974,15 +1024,15 @@ int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const flo
   if (L->max_U <= 48) {
     PL_LAUNCH(slice_dot_kernel<48>, grid, kThreads, sizeof(float) * 48 * kCW + ent, st, val, Cc, L->n, d1,
               L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, other, other_stride, out,
-              out_stride, coef);
+              out_stride, coef, J);
   } else if (L->max_U <= 96) {
     PL_LAUNCH(slice_dot_kernel<96>, grid, kThreads, sizeof(float) * 96 * kCW + ent, st, val, Cc, L->n, d1,
               L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, other, other_stride, out,
-              out_stride, coef);
+              out_stride, coef, J);
   } else {
     PL_LAUNCH(slice_dot_kernel<160>, grid, kThreads, sizeof(float) * 160 * kCW + ent, st, val, Cc, L->n, d1,
               L->rec_slice, L->vid, L->useg, L->tile_off, L->tile_U, denom, other, other_stride, out,
-              out_stride, coef);
+              out_stride, coef, J);
   }
   return PL_OK;
 }

@@ -98,6 +98,24 @@ class PermutohedralLattice:
 
     __call__ = filter
 
+    def filter_dot_multi(self, src, other, out, rowscale, coef=1.0):
+        """``out[p, j] += coef * <filter(src * rowscale[:, j, None])[p], other[p]>`` for all the
+        J = 5 columns of ``rowscale [n, 5]`` in one pass (d = 5 lattices; gaussian_matrix.py:450-463)."""
+        self._check_rows(src, "src")
+        self._check_rows(other, "other")
+        src, other = _rowmajor(src), _rowmajor(other)
+        c = int(src.shape[1])
+        J = int(rowscale.shape[1])
+        if (other.shape[1] != c or tuple(out.shape) != (self.n, J) or tuple(rowscale.shape) != (self.n, J)
+                or rowscale.stride(1) != 1 or out.stride(1) != 1 or rowscale.dtype != torch.float32):
+            raise ValueError("filter_dot_multi: other [n, C], rowscale / out [n, J] with unit column stride")
+        with torch.cuda.device(self.device):
+            N.check(N.lib().pl_lattice_apply_dot_multi(
+                self._h, C.c_void_p(src.data_ptr()), src.stride(0), c, C.c_void_p(rowscale.data_ptr()),
+                rowscale.stride(0), J, C.c_void_p(other.data_ptr()), other.stride(0),
+                C.c_void_p(out.data_ptr()), out.stride(0), float(coef), N.stream_ptr(self.device)))
+        return out
+
     def filter_dot(self, src, other, out, rowscale=None, coef=1.0):
         """``out[p] += coef * <filter(src * rowscale[:, None])[p], other[p]>`` without materialising
         the scaled source or the filtered rows (the guide gradient, gaussian_matrix.py:450-463).

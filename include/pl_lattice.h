@@ -120,6 +120,14 @@ int pl_lattice_apply(pl_lattice* lat, const float* src_dev, int64_t src_stride, 
 int pl_lattice_apply_dot(pl_lattice* lat, const float* src_dev, int64_t src_stride, int C,
                          const float* rowscale_dev, int64_t rowscale_stride, const float* other_dev,
                          int64_t other_stride, float* out_dev, int64_t out_stride, float coef, void* stream);
+/* The same for J row factors at once (the d = 5 features of the guide, J = 5 only; d = 5 lattices):
+ *   out[p * out_stride + j] += coef * <filter(src * rowscale[p * rowscale_stride + j])[p], other[p]>,  j < J.
+ * The source rows are staged and gathered once for all J sources, the rows of `other` once for all J
+ * contractions. */
+int pl_lattice_apply_dot_multi(pl_lattice* lat, const float* src_dev, int64_t src_stride, int C,
+                               const float* rowscale_dev, int64_t rowscale_stride, int J,
+                               const float* other_dev, int64_t other_stride, float* out_dev,
+                               int64_t out_stride, float coef, void* stream);
 
 /* ---- the reference's call shape ------------------------------------------- */
 

@@ -184,6 +184,23 @@ def test_filter_dot_matches_composition(native, oracle, n, d, C, scale):
     assert _relerr(out.cpu().numpy(), want) < TOL
 
 
+@pytest.mark.parametrize("n,C,scale", [(3000, 64, 4.0), (2500, 100, 12.0), (777, 8, 2.0), (130, 256, 2.0),
+                                       (5000, 68, 30.0)])
+def test_filter_dot_multi_matches_single(native, n, C, scale):
+    """All five row factors in one pass (pl_lattice_apply_dot_multi) against five single passes."""
+    src, ref = _rand(n, 5, C, scale, seed=n + C + 1)
+    rng = np.random.default_rng(12)
+    other = _cuda(rng.standard_normal((n, C)).astype(np.float32))
+    rs = _cuda(rng.standard_normal((n, 5)).astype(np.float32))
+    out0 = rng.standard_normal((n, 5)).astype(np.float32)
+    lat = native.PermutohedralLattice(_cuda(ref))
+    one, many = _cuda(out0), _cuda(out0)
+    for j in range(5):
+        lat.filter_dot(_cuda(src), other, one[:, j], rowscale=rs[:, j], coef=-1.5)
+    lat.filter_dot_multi(_cuda(src), other, many, rs, coef=-1.5)
+    assert _relerr(many.cpu().numpy(), one.cpu().numpy()) < 2e-5
+
+
 def test_guide_gradient_contracted_path_matches_slab_path(native):
     """_grad_reference with the contracted filter (L % 4 == 0) against its own slab form (the reference's
     arithmetic per column, checked against the golden gradients elsewhere)."""
