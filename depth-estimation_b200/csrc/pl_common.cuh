@@ -109,6 +109,7 @@ int lattice_build(Lattice* L, const float* ref, cudaStream_t st, const GuideSrc*
 int lattice_build_tiles(Lattice* L, cudaStream_t st);
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
                 cudaStream_t st, const float* rowscale = nullptr, int64_t rs_stride = 0, int J = 1);
+int splat_sorted(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val, cudaStream_t st);
 int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const float* other,
                     int64_t other_stride, float* out, int64_t out_stride, float coef, cudaStream_t st,
                     int J = 1);

@@ -410,8 +410,12 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
   // per-entry kernels with warp-aggregated atomics win (measured at 1 MP: C = 4..16 2-2.7x,
   // C = 32 1.3x; C = 64 the tile kernels are 1.8x ahead)
   const bool tiled = (VEC == 4) && !(flags & PL_APPLY_FLAT_KERNELS) && L->ntiles > 0 && Cc > 32;
+  static const bool no_sorted = getenv("PL_SPLAT_NO_SORTED") != nullptr;
   if (tiled) {
     PL_TRY(splat_tiled(L, src, src_stride, Cc, cur, st));
+  } else if ((Cc <= 3 || (VEC == 4 && Cc == 4)) && !no_sorted &&
+             !(flags & PL_APPLY_FLAT_KERNELS) && L->ntiles > 0) {
+    PL_TRY(splat_sorted(L, src, src_stride, Cc, cur, st));
   } else {
     const int V = Cc / VEC;
     if (V == 1) {

@@ -703,6 +703,104 @@ splat_pipe_kernel(const float* __restrict__ src, int64_t src_stride, int Cc, int
 }
 
 // ---------------------------------------------------------------------------
+// splat for narrow inputs (1..4 channels), over the tile's vertex-sorted entry record: one thread per
+// entry, segmented warp scan over the runs of equal vertex ids (contiguous after the sort, across all
+// d+1 remainders), one atomic per run and channel.   permutohedral.h:452-455
+// ---------------------------------------------------------------------------
+template <int CH>
+__global__ void __launch_bounds__(kThreads)
+splat_sorted_kernel(const float* __restrict__ src, int64_t src_stride, int64_t n, int d1,
+                    const uint8_t* __restrict__ rec_splat, float* __restrict__ val) {
+  __shared__ float s_src[kTile * CH];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int64_t tile = blockIdx.x;
+  const int TE = kTile * d1;
+  const int64_t p0 = tile * kTile;
+  const int rows = (int)min((int64_t)kTile, n - p0);
+  for (int i = tid; i < kTile * CH; i += kThreads) {
+    const int r = i / CH, c = i - r * CH;
+    s_src[i] = r < rows ? src[(p0 + r) * src_stride + c] : 0.f;
+  }
+  __syncthreads();
+  const float* rp_w = reinterpret_cast<const float*>(rec_splat + tile * (int64_t)TE * 9);
+  const int32_t* rp_vid = reinterpret_cast<const int32_t*>(rp_w + TE);
+  const uint8_t* rp_pix = reinterpret_cast<const uint8_t*>(rp_vid + TE);
+  for (int base = 0; base < TE; base += kThreads) {   // TE is a multiple of 128: warps stay whole
+    const int e = base + tid;
+    const bool ok = e < TE;
+    const float w = ok ? rp_w[e] : 0.f;
+    const int v = ok ? rp_vid[e] : -1 - lane;
+    const int pix = ok ? (int)rp_pix[e] : 0;
+    float x[CH];
+#pragma unroll
+    for (int c = 0; c < CH; c++) x[c] = w * s_src[pix * CH + c];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int vo = __shfl_up_sync(0xffffffffu, v, o);
+      const bool same = lane >= o && vo == v;
+#pragma unroll
+      for (int c = 0; c < CH; c++) {
+        const float y = __shfl_up_sync(0xffffffffu, x[c], o);
+        if (same) x[c] += y;
+      }
+    }
+    const int vn = __shfl_down_sync(0xffffffffu, v, 1);
+    if (ok && (lane == 31 || vn != v)) {
+      if (CH == 4) {
+        red_add_v4(val + (int64_t)v * 4, make_float4(x[0], x[1 % CH], x[2 % CH], x[3 % CH]));
+      } else {
+#pragma unroll
+        for (int c = 0; c < CH; c++) atomicAdd(val + (int64_t)v * CH + c, x[c]);
+      }
+    }
+  }
+}
+
+// the same for 4, 8 or 16 channels: V float4 lanes per entry, 32 / V entries per warp step
+template <int V>
+__global__ void __launch_bounds__(kThreads)
+splat_sorted_vec_kernel(const float* __restrict__ src, int64_t src_stride, int64_t n, int d1,
+                        const uint8_t* __restrict__ rec_splat, float* __restrict__ val) {
+  __shared__ __align__(16) float s_src[kTile * 4 * V];
+  constexpr int CH = 4 * V;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int64_t tile = blockIdx.x;
+  const int TE = kTile * d1;
+  const int64_t p0 = tile * kTile;
+  const int rows = (int)min((int64_t)kTile, n - p0);
+  for (int i = tid; i < kTile * V; i += kThreads) {
+    const int r = i / V, c = i - r * V;
+    reinterpret_cast<float4*>(s_src)[i] =
+        r < rows ? *reinterpret_cast<const float4*>(src + (p0 + r) * src_stride + 4 * c)
+                 : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  __syncthreads();
+  const float* rp_w = reinterpret_cast<const float*>(rec_splat + tile * (int64_t)TE * 9);
+  const int32_t* rp_vid = reinterpret_cast<const int32_t*>(rp_w + TE);
+  const uint8_t* rp_pix = reinterpret_cast<const uint8_t*>(rp_vid + TE);
+  const int li = tid % V;
+  for (int base = 0; base < TE; base += kThreads / V) {   // (kThreads / V) divides TE: warps stay whole
+    const int e = base + tid / V;
+    const bool ok = e < TE;
+    const float w = ok ? rp_w[e] : 0.f;
+    const int v = ok ? rp_vid[e] : -1 - lane;
+    const int pix = ok ? (int)rp_pix[e] : 0;
+    float4 x = reinterpret_cast<const float4*>(s_src)[pix * V + li];
+    x.x *= w; x.y *= w; x.z *= w; x.w *= w;
+#pragma unroll
+    for (int o = V; o < 32; o <<= 1) {
+      const int vo = __shfl_up_sync(0xffffffffu, v, o);
+      const bool same = lane >= o && vo == v;
+      const float y0 = __shfl_up_sync(0xffffffffu, x.x, o), y1 = __shfl_up_sync(0xffffffffu, x.y, o);
+      const float y2 = __shfl_up_sync(0xffffffffu, x.z, o), y3 = __shfl_up_sync(0xffffffffu, x.w, o);
+      if (same) { x.x += y0; x.y += y1; x.z += y2; x.w += y3; }
+    }
+    const int vn = __shfl_down_sync(0xffffffffu, v, V);
+    if (ok && (lane + V >= 32 || vn != v)) red_add_v4(val + (int64_t)v * CH + 4 * li, x);
+  }
+}
+
+// ---------------------------------------------------------------------------
 // slice, tiled (+ fused epilogue).  grid = (tiles, channel blocks).  permutohedral.h:473-483
 //
 // 8 lanes per pixel row, 8 channels each (float4 indices l and l + 8), 4 rows per thread; the
@@ -1002,6 +1100,21 @@ int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, i
   if (L->max_U <= 96) PL_SLICE(false, 96);
   PL_SLICE(false, 160);
 #undef PL_SLICE
+}
+
+// narrow inputs: Cc in {1, 2, 3} (scalars) or 4 (one float4 lane per entry, 16-byte aligned rows);
+// measured against the per-pixel aggregation: C = 1 1.3-1.6x, C = 4 1.1-1.4x faster, C = 16 (four
+// lanes per entry) 1.1x slower, so wider inputs stay with splat_agg_kernel
+int splat_sorted(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val, cudaStream_t st) {
+  const int d1 = L->d + 1;
+  switch (Cc) {
+    case 1: PL_LAUNCH(splat_sorted_kernel<1>, (unsigned)L->ntiles, kThreads, 0, st, src, src_stride, L->n, d1, L->rec_splat, val); break;
+    case 2: PL_LAUNCH(splat_sorted_kernel<2>, (unsigned)L->ntiles, kThreads, 0, st, src, src_stride, L->n, d1, L->rec_splat, val); break;
+    case 3: PL_LAUNCH(splat_sorted_kernel<3>, (unsigned)L->ntiles, kThreads, 0, st, src, src_stride, L->n, d1, L->rec_splat, val); break;
+    case 4: PL_LAUNCH(splat_sorted_vec_kernel<1>, (unsigned)L->ntiles, kThreads, 0, st, src, src_stride, L->n, d1, L->rec_splat, val); break;
+    default: set_last_error("splat_sorted: C = %d", Cc); return PL_ERR_INVALID;
+  }
+  return PL_OK;
 }
 
 int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const float* other,
