@@ -224,6 +224,26 @@ def run_reference(args, rank, world):
     }))
 
 
+def _bind_to_gpu_numa_node(local_rank):
+    """One process per GPU: run (and first-touch the pinned e2e buffers) on the CPU cores next to the
+    GPU, so that N ranks staging 100 MB per frame do not all pull from one socket's memory.  Best
+    effort: returns the NUMA node or None."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local_rank)
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open(path + "/numa_node").read())
+        cpus = set()
+        for part in open(path + "/local_cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        if cpus:
+            os.sched_setaffinity(0, cpus & os.sched_getaffinity(0) or cpus)
+        return node
+    except Exception:
+        return None
+
+
 def run_ours(args, rank, local_rank, world):
     import numpy as np
     import torch
@@ -231,6 +251,7 @@ def run_ours(args, rank, local_rank, world):
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = _bind_to_gpu_numa_node(local_rank) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     import depth_estimation_b200 as pkg
@@ -444,7 +465,7 @@ def run_ours(args, rank, local_rank, world):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "h": H, "w": W, "labels": L, "mf_iters": NITERS,
-                       "d": D, "frames_per_step_per_gpu": 1, "parallelism": f"image-parallel x{world}",
+                       "d": D, "frames_per_step_per_gpu": 1, "parallelism": f"image-parallel x{world}", "rank0_numa_node": numa,
                        "l2": "flushed between timed steps (256 MiB write)",
                        "step": "lattice build + 5 fused mean-field iterations, inputs in HBM"},
             "e2e": {"value": e2e_value, "unit": "frames/s",
