@@ -227,10 +227,10 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
               for (int ks = 0; ks < kKB / 8; ks++) {
                 const uint64_t ad = a_cur + (uint64_t)(j * (kKB / 8) + ks) * a_k8;
                 const uint64_t bd = b_cur + (uint64_t)ks * b_k8;
-                // lo*hi, hi*lo, hi*hi
+                // lo*hi, hi*hi, hi*lo
                 tc::mma_tf32_ss(acc, ad + a_lo_off, bd, idesc, (kc | j | ks) != 0);
-                tc::mma_tf32_ss(acc, ad, bd + b_lo_off, idesc, true);
                 tc::mma_tf32_ss(acc, ad, bd, idesc, true);
+                tc::mma_tf32_ss(acc, ad, bd + b_lo_off, idesc, true);
               }
             }
             tc::mma_commit(&bar_free[slot]);   // ring slot free once these MMAs have read it
