@@ -21,7 +21,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import _native as N
-from .gaussian_matrix import BatchedAdjacency, lattice_for, _cached
+from .gaussian_matrix import BatchedAdjacency, lattice_for, flat_guide
 
 
 def gaussian_weights(f):
@@ -136,9 +136,7 @@ class _MeanFieldLoop(torch.autograd.Function):
         with torch.cuda.device(dev):
             N.check(N.lib().pl_nchw_to_nlc(C.c_void_p(E0c.data_ptr()), C.c_void_p(e0.data_ptr()),
                                            B, L, n, 1.0, st))
-        flat_refs = _cached(refs, lambda: refs.detach().reshape(B, d, -1).permute(0, 2, 1).contiguous())
-        if flat_refs.requires_grad:
-            flat_refs = flat_refs.detach()
+        flat_refs = flat_guide(refs)
         mu_t = mu.detach().t().contiguous()
         s = float(scale)
         qs = []
@@ -278,7 +276,7 @@ class CRFasRNN(nn.Module):
             any(p.requires_grad for p in self.Mu.parameters()) or
             (torch.is_tensor(confidence) and confidence.requires_grad))
         if not (self.fused and not needs_grad and isinstance(self.Mu, charb) and self.niters > 0):
-            out = self.forward(refs, logits, confidence if torch.is_tensor(confidence) else None, labels)
+            out = self.forward(refs, logits, confidence, labels)
             probs = F.softmax(out, dim=1)
             lab = (torch.arange(out.shape[1], dtype=torch.float32, device=out.device)
                    if labels is None else labels.reshape(-1).to(out.device))
@@ -289,8 +287,7 @@ class CRFasRNN(nn.Module):
         dev = E0.device
         with torch.no_grad():
             mu, scale = self._compat_cached(L, labels, dev)
-            flat_refs = _cached(
-                refs, lambda: refs.reshape(B, d, -1).permute(0, 2, 1).contiguous())
+            flat_refs = flat_guide(refs)
             E0c = E0.float().contiguous()
             e0_nl = torch.empty((B, n, L), dtype=torch.float32, device=dev)
             with torch.cuda.device(dev):
@@ -303,17 +300,22 @@ class CRFasRNN(nn.Module):
         return torch.stack(maps).view(B, 1, H, W)
 
     def _compat_cached(self, L, labels, dev):
-        """(Mu matrix on the device, exp(s) as a host float), recomputed only when gamma / s /
-        labels change -- reading exp(s) back costs a host-device synchronisation per call."""
+        """(Mu matrix on the device, exp(s) as a host float).  With the default labels
+        (``arange(L)``) the pair is recomputed only when gamma / s change -- reading exp(s) back
+        costs a host-device synchronisation per call.  With caller-supplied ``labels`` the L x L
+        matrix is rebuilt on every call (it is tiny): a key on the labels tensor's address would
+        match a recycled allocation holding different values (CRFdepthUpsampler builds a fresh
+        ``linspace`` per frame), so only exp(s) is cached on that path."""
         key = (L, str(dev), self.Mu.gamma._version, self.Mu.s._version,
-               self.Mu.gamma.data_ptr(), self.Mu.s.data_ptr(),
-               None if labels is None else (labels.data_ptr(), labels._version, tuple(labels.shape)))
+               self.Mu.gamma.data_ptr(), self.Mu.s.data_ptr())
         hit = getattr(self, "_compat_cache", None)
         if hit is None or hit[0] != key:
-            mu = self.Mu.matrix(L, labels, dev).float().contiguous()
+            mu = self.Mu.matrix(L, None, dev).float().contiguous()
             scale = float(torch.exp(self.Mu.s))
             hit = (key, mu, scale)
             self._compat_cache = hit
+        if labels is not None:
+            return self.Mu.matrix(L, labels.to(dev), dev).float().contiguous(), hit[2]
         return hit[1], hit[2]
 
     def _forward_fused(self, refs, E0, labels):
@@ -322,8 +324,7 @@ class CRFasRNN(nn.Module):
         dev = E0.device
         with torch.no_grad():
             mu, scale = self._compat_cached(L, labels, dev)
-            flat_refs = _cached(
-                refs, lambda: refs.reshape(B, d, -1).permute(0, 2, 1).contiguous())
+            flat_refs = flat_guide(refs)
             E0c = E0.float().contiguous()
             e0_nl = torch.empty((B, n, L), dtype=torch.float32, device=dev)
             st = N.stream_ptr(dev)

@@ -29,9 +29,17 @@ latticefilter = _lattice.filter  # gaussian_matrix.py:16
 # One lattice per live feature tensor.  An entry PINS the tensor it was built
 # from, so its storage cannot be freed and handed to a different tensor while
 # the entry lives; the key also carries the version counter, so an in-place
-# update of the features (through any view) invalidates it.
+# update of the features (through any view) invalidates it.  Only DETACHED
+# values are stored (flattened guides without autograd history, lattices); the
+# differentiable flattening lives outside the cache (_FlattenGuide below), so a
+# no-grad call can never hand a grad-less guide to a later training call.
+#
+# The cache is a small LRU: a frame holds two entries (flattened guide and its
+# lattice) per image, and a 2.9 MP lattice pins ~0.3 GB, so the default keeps
+# only a few frames alive.  set_lattice_cache_limit() raises it for callers
+# that revisit many guides (e.g. several Laplacians side by side).
 _CACHE = {}
-_CACHE_MAX = 128
+_CACHE_MAX = 8
 
 
 def _key(t):
@@ -40,10 +48,11 @@ def _key(t):
 
 def _cached(t, build):
     key = _key(t)
-    hit = _CACHE.get(key)
+    hit = _CACHE.pop(key, None)
     if hit is not None:
+        _CACHE[key] = hit                      # most recently used goes last
         return hit[1]
-    if len(_CACHE) >= _CACHE_MAX:
+    while len(_CACHE) >= _CACHE_MAX:
         old = _CACHE.pop(next(iter(_CACHE)))[1]
         if isinstance(old, PermutohedralLattice):
             old.close()
@@ -57,18 +66,47 @@ def lattice_for(ref):
     return _cached(ref, lambda: PermutohedralLattice(ref.detach()))
 
 
+def flat_guide(guide_imgs):
+    """Detached pixel-major copy ``[B, n, d]`` of a guide batch ``[B, d, h, w]``
+    (gaussian_matrix.py:348-349), cached per guide tensor so its lattices are found again on
+    every mean-field iteration and in the backward pass."""
+    bs, d = guide_imgs.shape[:2]
+    return _cached(guide_imgs,
+                   lambda: guide_imgs.detach().reshape(bs, d, -1).permute(0, 2, 1).contiguous())
+
+
+class _FlattenGuide(Function):
+    """Differentiable ``guide.reshape(B, d, -1).permute(0, 2, 1)`` whose forward value is a view of
+    the cached detached copy (same storage, shape and version counter -> the same cache key, so the
+    lattice built for it is reused by every iteration), and whose backward is the inverse permute."""
+
+    @staticmethod
+    def forward(ctx, guide_imgs):
+        ctx.shape = tuple(guide_imgs.shape)
+        flat = flat_guide(guide_imgs)
+        return flat.view_as(flat)
+
+    @staticmethod
+    def backward(ctx, grad):
+        return grad.permute(0, 2, 1).reshape(ctx.shape)
+
+
 def set_lattice_cache_limit(entries):
-    """Bound the cache (oldest entries are destroyed first).  A frame holds two entries (the
-    flattened guide and its lattice); a streaming caller that keeps k frames in flight wants
-    2k so device memory is returned to the pool as it goes."""
+    """Bound the cache (least recently used entries are destroyed first).  A frame holds two
+    entries per image (the flattened guide and its lattice); a streaming caller that keeps k
+    frames in flight wants 2k so device memory is returned to the pool as it goes."""
     global _CACHE_MAX
     _CACHE_MAX = max(2, int(entries))
+    while len(_CACHE) > _CACHE_MAX:
+        old = _CACHE.pop(next(iter(_CACHE)))[1]
+        if isinstance(old, PermutohedralLattice):
+            old.close()
 
 
 def forget(guide_imgs):
     """Drop (and free) what the cache holds for one guide batch ``[B, d, h, w]``: its flattened
     copy and the lattices built from it.  For streaming callers: call once the frame's work
-    has completed on the device."""
+    has been enqueued (the lattice's memory is released in stream order)."""
     hit = _CACHE.pop(_key(guide_imgs), None)
     if hit is None:
         return
@@ -260,10 +298,13 @@ class BatchedAdjacency(nn.Module):
         bs, L, h, w = src_imgs.shape
         bs, d, h, w = guide_imgs.shape
         flat_srcs = src_imgs.reshape(bs, L, -1).permute(0, 2, 1).contiguous()
-        # the same guide tensor comes back on every mean-field iteration
-        # (crf_module.py:101): flatten it once so its lattices are found again
-        flat_refs = _cached(
-            guide_imgs, lambda: guide_imgs.reshape(bs, d, -1).permute(0, 2, 1).contiguous())
+        # the same guide tensor comes back on every mean-field iteration (crf_module.py:101):
+        # it is flattened once (detached, cached) so its lattices are found again; when the guide
+        # needs a gradient the autograd edge is added on top of the cached value
+        if torch.is_grad_enabled() and guide_imgs.requires_grad:
+            flat_refs = _FlattenGuide.apply(guide_imgs)
+        else:
+            flat_refs = flat_guide(guide_imgs)
         filtered_imgs = BatchedLatticeFilter.apply(flat_srcs, flat_refs, self.num_threads) \
             .permute(0, 2, 1).reshape(src_imgs.shape)
         return filtered_imgs - src_imgs

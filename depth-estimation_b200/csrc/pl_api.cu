@@ -158,10 +158,6 @@ int pl_lattice_create(const float* ref_dev, int64_t n, int d, uint32_t flags, vo
     pl::set_last_error("pl_lattice_create: bad arguments (n=%lld, d=%d)", (long long)n, d);
     return PL_ERR_INVALID;
   }
-  if (flags & PL_BUILD_REF_GROW_QUIRK) {
-    pl::set_last_error("PL_BUILD_REF_GROW_QUIRK is not implemented yet");
-    return PL_ERR_INVALID;
-  }
   PL_TRY(pl::check_device());
   cudaStream_t st = (cudaStream_t)stream;
   Lattice* L = new (std::nothrow) Lattice();
@@ -169,6 +165,7 @@ int pl_lattice_create(const float* ref_dev, int64_t n, int d, uint32_t flags, vo
   L->n = n;
   L->d = d;
   L->flags = flags;
+  L->last_stream = st;
   cudaGetDevice(&L->device);
   int r = pl::lattice_build(L, ref_dev, st);
   if (r != PL_OK) {
@@ -187,10 +184,6 @@ int pl_lattice_create_ijrgb(const float* rgb_planes_dev, int h, int w, float s_i
     pl::set_last_error("pl_lattice_create_ijrgb: bad arguments (h=%d, w=%d)", h, w);
     return PL_ERR_INVALID;
   }
-  if (flags & PL_BUILD_REF_GROW_QUIRK) {
-    pl::set_last_error("PL_BUILD_REF_GROW_QUIRK is not implemented yet");
-    return PL_ERR_INVALID;
-  }
   PL_TRY(pl::check_device());
   cudaStream_t st = (cudaStream_t)stream;
   Lattice* L = new (std::nothrow) Lattice();
@@ -198,6 +191,7 @@ int pl_lattice_create_ijrgb(const float* rgb_planes_dev, int h, int w, float s_i
   L->n = (int64_t)h * w;
   L->d = 5;
   L->flags = flags;
+  L->last_stream = st;
   cudaGetDevice(&L->device);
   pl::GuideSrc gs;
   gs.rgb = rgb_planes_dev; gs.h = h; gs.w = w; gs.s_ij = s_ij; gs.s_rgb = s_rgb;
@@ -212,7 +206,15 @@ int pl_lattice_create_ijrgb(const float* rgb_planes_dev, int h, int w, float s_i
 }
 
 void pl_lattice_destroy(pl_lattice* lat) {
-  if (lat) pl::lattice_release(reinterpret_cast<Lattice*>(lat), (cudaStream_t)0);
+  if (lat == nullptr) return;
+  Lattice* L = reinterpret_cast<Lattice*>(lat);
+  // stream-ordered release on the stream that used the lattice last (torch side streams are
+  // non-blocking: freeing on the legacy stream would not be ordered against them)
+  int cur = -1;
+  cudaGetDevice(&cur);
+  if (cur != L->device) cudaSetDevice(L->device);
+  pl::lattice_release(L, L->last_stream);
+  if (cur >= 0 && cur != L->device) cudaSetDevice(cur);
 }
 
 int64_t pl_lattice_num_points(const pl_lattice* lat) { return reinterpret_cast<const Lattice*>(lat)->n; }
@@ -227,6 +229,7 @@ int pl_lattice_apply(pl_lattice* lat, const float* src_dev, int64_t src_stride, 
                      int64_t dst_stride, int C, const float* sub_dev, int64_t sub_stride,
                      const float* add_dev, int64_t add_stride, uint32_t flags, void* stream) {
   if (lat == nullptr) return PL_ERR_INVALID;
+  reinterpret_cast<Lattice*>(lat)->last_stream = (cudaStream_t)stream;
   return pl::lattice_apply(reinterpret_cast<Lattice*>(lat), src_dev, src_stride, dst_dev,
                            dst_stride, C, sub_dev, sub_stride, add_dev, add_stride, flags,
                            (cudaStream_t)stream);
@@ -236,6 +239,7 @@ int pl_lattice_apply_dot(pl_lattice* lat, const float* src_dev, int64_t src_stri
                          const float* rowscale_dev, int64_t rowscale_stride, const float* other_dev,
                          int64_t other_stride, float* out_dev, int64_t out_stride, float coef, void* stream) {
   if (lat == nullptr) return PL_ERR_INVALID;
+  reinterpret_cast<Lattice*>(lat)->last_stream = (cudaStream_t)stream;
   return pl::lattice_apply_dot(reinterpret_cast<Lattice*>(lat), src_dev, src_stride, C, rowscale_dev,
                                rowscale_stride, other_dev, other_stride, out_dev, out_stride, coef,
                                (cudaStream_t)stream);
@@ -246,6 +250,7 @@ int pl_lattice_apply_dot_multi(pl_lattice* lat, const float* src_dev, int64_t sr
                                const float* other_dev, int64_t other_stride, float* out_dev,
                                int64_t out_stride, float coef, void* stream) {
   if (lat == nullptr) return PL_ERR_INVALID;
+  reinterpret_cast<Lattice*>(lat)->last_stream = (cudaStream_t)stream;
   return pl::lattice_apply_dot(reinterpret_cast<Lattice*>(lat), src_dev, src_stride, C, rowscale_dev,
                                rowscale_stride, other_dev, other_stride, out_dev, out_stride, coef,
                                (cudaStream_t)stream, J);
@@ -254,7 +259,8 @@ int pl_lattice_apply_dot_multi(pl_lattice* lat, const float* src_dev, int64_t sr
 int pl_filter(const float* src_dev, const float* ref_dev, float* dst_dev, int64_t n, int C, int d,
               void* stream) {
   pl_lattice* lat = nullptr;
-  PL_TRY(pl_lattice_create(ref_dev, n, d, PL_BUILD_DEFAULT, stream, &lat));
+  // the reference's own call shape: reproduce its table-growth behaviour too
+  PL_TRY(pl_lattice_create(ref_dev, n, d, PL_BUILD_REF_GROW_QUIRK, stream, &lat));
   int r = pl_lattice_apply(lat, src_dev, C, dst_dev, C, C, nullptr, 0, nullptr, 0,
                            PL_APPLY_DEFAULT, stream);
   pl::lattice_release(reinterpret_cast<Lattice*>(lat), (cudaStream_t)stream);
@@ -430,6 +436,7 @@ static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT
   }
   Lattice* Lt = reinterpret_cast<Lattice*>(lat);
   cudaStream_t st = (cudaStream_t)stream;
+  Lt->last_stream = st;
   const int64_t n = Lt->n;
   if (niters == 0) {
     PL_CUDA(cudaMemcpyAsync(e_out_dev, e0_dev, sizeof(float) * (size_t)n * L,
@@ -597,6 +604,7 @@ int pl_nlc_to_nchw(const float* src_dev, float* dst_dev, int64_t batch, int C, i
 
 int pl_lattice_export(const pl_lattice* lat, int what, void* dst_dev, void* stream) {
   if (lat == nullptr || dst_dev == nullptr) return PL_ERR_INVALID;
+  const_cast<Lattice*>(reinterpret_cast<const Lattice*>(lat))->last_stream = (cudaStream_t)stream;
   return pl::lattice_export(reinterpret_cast<const Lattice*>(lat), what, dst_dev,
                             (cudaStream_t)stream);
 }

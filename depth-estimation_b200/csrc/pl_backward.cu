@@ -167,11 +167,10 @@ int mf_backward_step(float* dp, const float* q, const float* mu, float* de0, flo
   }
   if (n == 0) return PL_OK;
   const size_t smem = sizeof(float) * (2 * (size_t)kTile * kPI + kL * kL);
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.need()) {
     PL_CUDA(cudaFuncSetAttribute(mf_backward_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem));
-    attr_done = true;
   }
   const int64_t ntiles = (n + kTile - 1) / kTile;
   const int64_t cap = 2 * PL_SM_COUNT;

@@ -363,7 +363,8 @@ __global__ void __launch_bounds__(kScanThreads)
 assign_kernel(const unsigned long long* __restrict__ table, const int32_t* __restrict__ slot,
               uint64_t E, const uint32_t* __restrict__ chunk_offset,
               const int16_t* __restrict__ greedy, const int8_t* __restrict__ rank,
-              int32_t* __restrict__ slot_vid, int16_t* __restrict__ vkeys) {
+              int32_t* __restrict__ slot_vid, int16_t* __restrict__ vkeys,
+              uint32_t* __restrict__ first_e, int32_t* __restrict__ vslot) {
   __shared__ uint32_t warp_cnt[kScanThreads / 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint64_t base = (uint64_t)blockIdx.x * kScanChunk;
@@ -385,6 +386,10 @@ assign_kernel(const unsigned long long* __restrict__ table, const int32_t* __res
     if (first) {
       const uint32_t v = running + before + __popc(bal & ((1u << lane) - 1u));
       slot_vid[slot[e]] = (int32_t)v;
+      if (first_e != nullptr) {   // growth-quirk replay: where and when each vertex was created
+        first_e[v] = (uint32_t)e;
+        vslot[v] = slot[e];
+      }
       int16_t key[D];
       const uint64_t p = e / (D + 1);
       load_key<D>(greedy, rank, (int64_t)p, (int)(e - p * (D + 1)), key);
@@ -421,10 +426,13 @@ __device__ __forceinline__ int32_t table_find(const unsigned long long* __restri
     if (cur == kEmpty) return -1;
     if ((uint32_t)(cur >> 32) == fp) {
       const int32_t v = slot_vid[h];
+      // slot_key: vertex whose stored key describes this slot (the growth-quirk replay may point
+      // the slot at a later copy of the same key, or at nothing: v < 0 encodes -(key vertex) - 2)
+      const int32_t kv = v >= 0 ? v : -(v + 2);
       bool same = true;
 #pragma unroll
-      for (int i = 0; i < D; i++) same = same && (vkeys[(int64_t)v * D + i] == key[i]);
-      if (same) return v;
+      for (int i = 0; i < D; i++) same = same && (vkeys[(int64_t)kv * D + i] == key[i]);
+      if (same) return v >= 0 ? v : -1;
     }
     h = (h + 1) & mask;
   }
@@ -457,6 +465,361 @@ neighbour_kernel(const unsigned long long* __restrict__ table,
       nbr[(int64_t)j * M + v] = make_int2(a < 0 ? (int)M : a, b < 0 ? (int)M : b);
     }
   }
+}
+
+// ---------------------------------------------------------------------------
+// 6. the reference's hash-growth quirk (PL_BUILD_REF_GROW_QUIRK)       permutohedral.h:59-62,101-155
+//
+// HashTablePermutohedral::lookup computes h = hash % capacity and then lookupOffset() may grow()
+// the table before it probes from h.  The ONE lookup that triggers each doubling (the first
+// lookup after `filled` reaches capacity/2 - 1) therefore probes from a slot computed with the
+// old capacity.  If bit log2(old capacity) of its hash is set, it misses an existing key (or
+// parks a new key where later lookups cannot find it) and creates an extra vertex with a
+// duplicate key.  After the NEXT doubling the rehash walks the old slots in ascending order, so
+// the parked copy (lower slot) is re-placed ahead of the regular one and becomes the copy every
+// later lookup finds.  Everything else about the table (slot positions, probe lengths) is
+// invisible to the filter.
+//
+// The clean build above yields one vertex per distinct key in first-touch order.  The replay
+// below walks the <= 17 doubling events in scanline order, decides for each what the reference
+// did, and emits a patch: the creation entries of the extra vertices, and for the handful of
+// "special" keys a timeline (from entry x on, lookups return the copy created at entry c).
+// Assumptions (both hold unless a probe run is >= capacity/2 long or wraps round the table end,
+// probability ~1e-4 per doubling on a table that is at most a quarter full): the stale probe
+// reaches an empty slot before a matching key, and slot order of two copies = order of their
+// home slots.  Checked against the unmodified reference in tests/ (M, vertex ids, keys,
+// neighbours bit-exact).
+// ---------------------------------------------------------------------------
+constexpr int kQMaxExtra = 64;
+constexpr int kQMaxSpecial = 40;
+constexpr int kQMaxSegs = 160;
+constexpr uint32_t kQNone = 0xFFFFFFFFu;
+
+struct GrowQuirk {
+  int n_extras;
+  uint32_t extra_entry[kQMaxExtra];   // creation entries of the extra vertices, ascending
+  int32_t extra_vertex[kQMaxExtra];   // clean vertex (= key) each one duplicates
+  int32_t extra_id[kQMaxExtra];       // final vertex id
+  int n_special;
+  int32_t special_v[kQMaxSpecial];    // clean vertex ids with more than one copy / a parked copy
+  uint32_t special_live[kQMaxSpecial];    // creation entry of the copy lookups find at the end (kQNone: none)
+  uint32_t special_parked[kQMaxSpecial];  // copy that becomes live at the next doubling
+  int32_t special_live_id[kQMaxSpecial];  // final id of the live copy, -1 none
+  int n_segs;
+  int32_t seg_v[kQMaxSegs];
+  uint32_t seg_start[kQMaxSegs];      // from this entry on ...
+  uint32_t seg_copy[kQMaxSegs];       // ... lookups of seg_v return the copy created at this entry
+  int32_t seg_id[kQMaxSegs];          // final id of that copy
+  int blur_trigger;                   // the last doubling happens at the first lookup of blur()
+  unsigned long long blur_cap_old;
+  int error;                          // small tables exhausted
+};
+
+__device__ __forceinline__ unsigned long long ref_hash(const int16_t* key, int D) {
+  // permutohedral.h:109-116: size_t arithmetic, shorts sign-extended
+  unsigned long long k = 0;
+  for (int i = 0; i < D; i++) {
+    k += (unsigned long long)(long long)key[i];
+    k *= 2531011ull;
+  }
+  return k;
+}
+
+// number of elements of the ascending array a[0..n) that are < x  (<= x with `incl`)
+__device__ __forceinline__ uint32_t count_below(const uint32_t* a, uint32_t n, uint32_t x, bool incl) {
+  uint32_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    const uint32_t v = a[mid];
+    if (v < x || (incl && v == x)) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+
+template <int D>
+__global__ void __launch_bounds__(1024)
+grow_replay_kernel(const int32_t* __restrict__ vid, const uint32_t* __restrict__ first_e,
+                   const int16_t* __restrict__ greedy, const int8_t* __restrict__ rank,
+                   const int16_t* __restrict__ vkeys, uint32_t E, uint32_t M, GrowQuirk* out) {
+  __shared__ GrowQuirk q;
+  __shared__ unsigned long long cap;
+  __shared__ int phase;             // 0 run, 1 need next touch, 2 done
+  __shared__ int32_t touch_v;
+  __shared__ uint32_t touch_after, touch_found;
+  __shared__ int pend_special;      // special index whose second touch is unconfirmed, -1 none
+  __shared__ uint32_t pend_entry;
+  __shared__ int cur_special;
+  const int tid = threadIdx.x;
+
+  auto find_special = [&](int32_t v) {
+    for (int i = 0; i < q.n_special; i++)
+      if (q.special_v[i] == v) return i;
+    return -1;
+  };
+  auto add_seg = [&](int32_t v, uint32_t start, uint32_t copy) {
+    if (q.n_segs >= kQMaxSegs) { q.error = 1; return; }
+    q.seg_v[q.n_segs] = v; q.seg_start[q.n_segs] = start; q.seg_copy[q.n_segs] = copy;
+    q.n_segs++;
+  };
+  auto add_extra = [&](uint32_t e, int32_t v) {
+    if (q.n_extras >= kQMaxExtra) { q.error = 1; return; }
+    int i = q.n_extras++;
+    while (i > 0 && q.extra_entry[i - 1] > e) {
+      q.extra_entry[i] = q.extra_entry[i - 1];
+      q.extra_vertex[i] = q.extra_vertex[i - 1];
+      i--;
+    }
+    q.extra_entry[i] = e;
+    q.extra_vertex[i] = v;
+  };
+  auto remove_extra = [&](uint32_t e) {
+    int i = 0;
+    while (i < q.n_extras && q.extra_entry[i] != e) i++;
+    if (i == q.n_extras) return;
+    for (; i + 1 < q.n_extras; i++) {
+      q.extra_entry[i] = q.extra_entry[i + 1];
+      q.extra_vertex[i] = q.extra_vertex[i + 1];
+    }
+    q.n_extras--;
+  };
+  // entry at which `filled` first reaches T: the T-th smallest of first_e U extras (kQNone: never)
+  auto first_reach = [&](unsigned long long T) -> uint32_t {
+    if (T == 0) return 0;
+    const int m = q.n_extras;
+    if ((unsigned long long)M + (unsigned)m < T) return kQNone;
+    for (int j = 0; j <= m; j++) {      // j = extras among the T smallest creations
+      if ((unsigned long long)j > T) break;
+      const unsigned long long c = T - j;   // clean creations among them
+      if (c > M) continue;
+      const uint32_t last_clean = c > 0 ? first_e[c - 1] : 0u;
+      const uint32_t last_extra = j > 0 ? q.extra_entry[j - 1] : 0u;
+      if (j < m && c > 0 && !(last_clean < q.extra_entry[j])) continue;   // next extra would be inside
+      if (j < m && c == 0 && j > 0) { /* only extras: fine */ }
+      if (j > 0 && c < M && !(last_extra < first_e[c])) continue;        // next clean would be inside
+      if (c == 0 && j == 0) continue;
+      return c > 0 && (j == 0 || last_clean > last_extra) ? last_clean : last_extra;
+    }
+    return kQNone;
+  };
+
+  if (tid == 0) {
+    q.n_extras = 0; q.n_special = 0; q.n_segs = 0; q.blur_trigger = 0; q.blur_cap_old = 0; q.error = 0;
+    cap = 1ull << 15;    // permutohedral.h:36
+    pend_special = -1;
+    phase = 0;
+  }
+  __syncthreads();
+
+  for (;;) {
+    if (tid == 0) {
+      phase = 0;
+      const unsigned long long T = cap / 2 - 1;             // :62
+      uint32_t ec = first_reach(T);
+      if (ec == kQNone) {
+        phase = 2;
+      } else {
+        unsigned long long t = (unsigned long long)ec + 1;  // the lookup that grows the table
+        if (pend_special >= 0) {
+          if ((unsigned long long)pend_entry >= t) {
+            // the doubling comes first: the parked copy is live again before the key is touched,
+            // no second copy is created
+            remove_extra(pend_entry);
+            for (int i = 0; i < q.n_segs; i++)
+              if (q.seg_v[i] == q.special_v[pend_special] && q.seg_start[i] == pend_entry &&
+                  q.seg_copy[i] == pend_entry) {
+                for (int k = i; k + 1 < q.n_segs; k++) {
+                  q.seg_v[k] = q.seg_v[k + 1]; q.seg_start[k] = q.seg_start[k + 1];
+                  q.seg_copy[k] = q.seg_copy[k + 1];
+                }
+                q.n_segs--;
+                break;
+              }
+            q.special_live[pend_special] = kQNone;
+            ec = first_reach(T);
+            t = (unsigned long long)ec + 1;
+          }
+          pend_special = -1;
+        }
+        if (ec == kQNone) {
+          phase = 2;
+        } else if (t >= E) {
+          // the table doubles at the first lookup of blur(): parked copies take over there
+          q.blur_trigger = 1;
+          q.blur_cap_old = cap;
+          for (int i = 0; i < q.n_special; i++)
+            if (q.special_parked[i] != kQNone) {
+              q.special_live[i] = q.special_parked[i];
+              q.special_parked[i] = kQNone;
+            }
+          cap *= 2;
+          phase = 2;
+        } else {
+          const uint32_t te = (uint32_t)t;
+          for (int i = 0; i < q.n_special; i++)
+            if (q.special_parked[i] != kQNone) {
+              q.special_live[i] = q.special_parked[i];
+              add_seg(q.special_v[i], te, q.special_parked[i]);
+              q.special_parked[i] = kQNone;
+            }
+          const unsigned long long cap_old = cap;
+          cap *= 2;
+          const int32_t v = vid[te];
+          const unsigned long long H = ref_hash(vkeys + (int64_t)v * D, D);
+          int si = find_special(v);
+          const uint32_t fe = first_e[v];
+          uint32_t live = si >= 0 ? q.special_live[si] : (fe < te ? fe : kQNone);
+          if ((H % cap_old) == (H % cap)) {
+            // regular lookup; a special key nobody can find gets its regular copy here
+            if (si >= 0 && live == kQNone) {
+              add_extra(te, v);
+              q.special_live[si] = te;
+              add_seg(v, te, te);
+            }
+          } else {
+            if (si < 0) {
+              if (q.n_special >= kQMaxSpecial) { q.error = 1; phase = 2; }
+              else {
+                si = q.n_special++;
+                q.special_v[si] = v;
+                q.special_live[si] = live;
+                q.special_parked[si] = kQNone;
+                if (live != kQNone) add_seg(v, live, live);
+              }
+            }
+            if (si >= 0) {
+              if (fe != te) add_extra(te, v);       // fe == te: this creation is the key's first touch
+              q.special_parked[si] = te;
+              add_seg(v, te, te);                   // the triggering entry itself uses the parked copy
+              if (live != kQNone) {
+                add_seg(v, te + 1, live);           // later lookups find the regular copy again
+              } else {
+                q.special_live[si] = kQNone;
+                phase = 1;                          // the next touch of the key creates a regular copy
+                touch_v = v;
+                touch_after = te;
+                cur_special = si;
+              }
+            }
+          }
+        }
+      }
+      if (q.error) phase = 2;
+      touch_found = kQNone;
+    }
+    __syncthreads();
+    if (phase == 2) break;
+    if (phase == 1) {
+      const int32_t v = touch_v;
+      for (unsigned long long base = (unsigned long long)touch_after + 1; base < E; base += 8192) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          const unsigned long long e = base + (unsigned long long)k * 1024 + tid;
+          if (e < E && vid[e] == v) atomicMin(&touch_found, (uint32_t)e);
+        }
+        __syncthreads();
+        const uint32_t found = touch_found;
+        __syncthreads();   // nobody starts the next chunk's atomics before everybody has read
+        if (found != kQNone) break;
+      }
+      if (tid == 0 && touch_found != kQNone) {
+        add_extra(touch_found, v);
+        add_seg(v, touch_found, touch_found);
+        q.special_live[cur_special] = touch_found;
+        pend_special = cur_special;
+        pend_entry = touch_found;
+      }
+    }
+    __syncthreads();
+  }
+
+  // final ids: id(copy created at entry c) = #clean creations < c + #extras < c
+  auto copy_id = [&](uint32_t c) -> int32_t {
+    return (int32_t)(count_below(first_e, M, c, false) + count_below(q.extra_entry, q.n_extras, c, false));
+  };
+  __syncthreads();
+  for (int i = tid; i < q.n_segs; i += blockDim.x) q.seg_id[i] = copy_id(q.seg_copy[i]);
+  for (int i = tid; i < q.n_extras; i += blockDim.x) q.extra_id[i] = copy_id(q.extra_entry[i]);
+  for (int i = tid; i < q.n_special; i += blockDim.x)
+    q.special_live_id[i] = q.special_live[i] == kQNone ? -1 : copy_id(q.special_live[i]);
+  __syncthreads();
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&q);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out);
+    for (int i = tid; i < (int)(sizeof(GrowQuirk) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+}
+
+// vertex id of entry e after the replay
+__device__ __forceinline__ int32_t quirk_vid(const GrowQuirk& q, const uint32_t* __restrict__ first_e,
+                                             int32_t v, uint32_t e) {
+  for (int i = 0; i < q.n_special; i++) {
+    if (q.special_v[i] != v) continue;
+    int best = -1;
+    for (int k = 0; k < q.n_segs; k++)    // latest segment that has started; ties: the later one
+      if (q.seg_v[k] == v && q.seg_start[k] <= e && (best < 0 || q.seg_start[k] >= q.seg_start[best]))
+        best = k;
+    if (best >= 0) return q.seg_id[best];
+  }
+  return v + (int32_t)count_below(q.extra_entry, (uint32_t)q.n_extras, first_e[v], false);
+}
+
+__global__ void __launch_bounds__(256)
+quirk_renumber_kernel(int32_t* __restrict__ vid, const uint32_t* __restrict__ first_e,
+                      const GrowQuirk* __restrict__ qg, uint64_t E) {
+  __shared__ GrowQuirk q;
+  for (int i = threadIdx.x; i < (int)(sizeof(GrowQuirk) / 4); i += blockDim.x)
+    reinterpret_cast<uint32_t*>(&q)[i] = reinterpret_cast<const uint32_t*>(qg)[i];
+  __syncthreads();
+  for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E;
+       e += (uint64_t)gridDim.x * blockDim.x)
+    vid[e] = quirk_vid(q, first_e, vid[e], (uint32_t)e);
+}
+
+// keys in the final numbering, and the hash table's slot -> vertex map pointed at the copy that
+// lookups find once splat() is over (what blur()'s neighbour lookups see)
+template <int D>
+__global__ void __launch_bounds__(256)
+quirk_keys_kernel(const int16_t* __restrict__ vkeys_clean, const uint32_t* __restrict__ first_e,
+                  const int32_t* __restrict__ vslot, const GrowQuirk* __restrict__ qg, int64_t M,
+                  int16_t* __restrict__ vkeys_final, int32_t* __restrict__ slot_vid) {
+  __shared__ GrowQuirk q;
+  for (int i = threadIdx.x; i < (int)(sizeof(GrowQuirk) / 4); i += blockDim.x)
+    reinterpret_cast<uint32_t*>(&q)[i] = reinterpret_cast<const uint32_t*>(qg)[i];
+  __syncthreads();
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < M + q.n_extras;
+       v += (int64_t)gridDim.x * blockDim.x) {
+    if (v < M) {
+      const int32_t id = (int32_t)v + (int32_t)count_below(q.extra_entry, (uint32_t)q.n_extras, first_e[v], false);
+#pragma unroll
+      for (int i = 0; i < D; i++) vkeys_final[(int64_t)id * D + i] = vkeys_clean[v * D + i];
+      int32_t live = id;
+      for (int i = 0; i < q.n_special; i++)
+        if (q.special_v[i] == (int32_t)v)
+          live = q.special_live_id[i] >= 0 ? q.special_live_id[i] : -(id + 2);   // unfindable: key vertex encoded
+      slot_vid[vslot[v]] = live;
+    } else {
+      const int x = (int)(v - M);
+      const int32_t src = q.extra_vertex[x];
+#pragma unroll
+      for (int i = 0; i < D; i++) vkeys_final[(int64_t)q.extra_id[x] * D + i] = vkeys_clean[(int64_t)src * D + i];
+    }
+  }
+}
+
+// blur()'s very first lookup (axis 0, vertex 0, the "minus" neighbour) is the one that grows the
+// table when splat() ended exactly on the threshold: it probes from the stale slot and, if the bit
+// is set, reports the neighbour as absent (create = false, permutohedral.h:516)
+template <int D>
+__global__ void quirk_blur_trigger_kernel(const GrowQuirk* __restrict__ qg,
+                                          const int16_t* __restrict__ vkeys, int64_t M,
+                                          int2* __restrict__ nbr) {
+  if (threadIdx.x != 0 || blockIdx.x != 0 || !qg->blur_trigger || M <= 0) return;
+  int16_t n1[D];
+#pragma unroll
+  for (int i = 0; i < D; i++) n1[i] = (int16_t)((i == 0) ? vkeys[i] - D : vkeys[i] + 1);
+  const unsigned long long H = ref_hash(n1, D);
+  if ((H % qg->blur_cap_old) != (H % (2 * qg->blur_cap_old))) nbr[0].x = (int)M;
 }
 
 // ---------------------------------------------------------------------------
@@ -559,15 +922,55 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
 
   int32_t* slot_vid = nullptr;
   PL_TRY(dev_alloc((void**)&slot_vid, sizeof(int32_t) * cap, st));
-  PL_TRY(dev_alloc((void**)&L->vkeys, sizeof(int16_t) * (size_t)M * D, st));
-  PL_TRY(dev_alloc((void**)&L->nbr, sizeof(int2) * (size_t)M * D1, st));
-  L->bytes += (int64_t)(sizeof(int16_t) * (size_t)M * D + sizeof(int2) * (size_t)M * D1);
-
+  // the reference's table only ever grows once it holds 2^14 - 1 vertices (permutohedral.h:36,62)
+  const bool quirk = (L->flags & PL_BUILD_REF_GROW_QUIRK) != 0 && M >= (1 << 14) - 1;
+  int16_t* vkeys_clean = nullptr;
+  uint32_t* first_e = nullptr;
+  int32_t* vslot = nullptr;
+  PL_TRY(dev_alloc((void**)&vkeys_clean, sizeof(int16_t) * (size_t)M * D, st));
+  if (quirk) {
+    PL_TRY(dev_alloc((void**)&first_e, sizeof(uint32_t) * (size_t)M, st));
+    PL_TRY(dev_alloc((void**)&vslot, sizeof(int32_t) * (size_t)M, st));
+  }
   PL_LAUNCH((assign_kernel<D>), nchunks, kScanThreads, 0, st, table, L->vid, E, chunk_count,
-            L->greedy, L->rank, slot_vid, L->vkeys);
+            L->greedy, L->rank, slot_vid, vkeys_clean, first_e, vslot);
   PL_LAUNCH(gather_kernel, grid_for(E, 256, 8), 256, 0, st, L->vid, slot_vid, E);
-  PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)M, 256, 8), 256, 0, st, table, slot_vid,
-            L->vkeys, (uint32_t)(cap - 1), M, L->nbr);
+  int64_t Mf = M;
+  if (quirk) {
+    GrowQuirk* qd = nullptr;
+    PL_TRY(dev_alloc((void**)&qd, sizeof(GrowQuirk), st));
+    PL_LAUNCH((grow_replay_kernel<D>), 1, 1024, 0, st, L->vid, first_e, L->greedy, L->rank,
+              vkeys_clean, (uint32_t)E, (uint32_t)M, qd);
+    int qres[1] = {0};
+    int qerr = 0;
+    PL_CUDA(cudaMemcpyAsync(qres, &qd->n_extras, sizeof(int), cudaMemcpyDeviceToHost, st));
+    PL_CUDA(cudaMemcpyAsync(&qerr, &qd->error, sizeof(int), cudaMemcpyDeviceToHost, st));
+    PL_CUDA(cudaStreamSynchronize(st));
+    if (qerr != 0) {
+      set_last_error("growth-quirk replay ran out of table space (%d extras)", qres[0]);
+      return PL_ERR_OVERFLOW;
+    }
+    Mf = M + qres[0];
+    PL_TRY(dev_alloc((void**)&L->vkeys, sizeof(int16_t) * (size_t)Mf * D, st));
+    PL_LAUNCH(quirk_renumber_kernel, grid_for(E, 256, 8), 256, 0, st, L->vid, first_e, qd, E);
+    PL_LAUNCH((quirk_keys_kernel<D>), grid_for((uint64_t)Mf, 256, 8), 256, 0, st, vkeys_clean, first_e,
+              vslot, qd, M, L->vkeys, slot_vid);
+    PL_TRY(dev_alloc((void**)&L->nbr, sizeof(int2) * (size_t)Mf * D1, st));
+    PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)Mf, 256, 8), 256, 0, st, table, slot_vid,
+              L->vkeys, (uint32_t)(cap - 1), Mf, L->nbr);
+    PL_LAUNCH((quirk_blur_trigger_kernel<D>), 1, 32, 0, st, qd, L->vkeys, Mf, L->nbr);
+    dev_free(qd, st);
+    dev_free(vkeys_clean, st);
+    dev_free(first_e, st);
+    dev_free(vslot, st);
+    L->M = Mf;
+  } else {
+    L->vkeys = vkeys_clean;
+    PL_TRY(dev_alloc((void**)&L->nbr, sizeof(int2) * (size_t)M * D1, st));
+    PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)M, 256, 8), 256, 0, st, table, slot_vid,
+              L->vkeys, (uint32_t)(cap - 1), M, L->nbr);
+  }
+  L->bytes += (int64_t)(sizeof(int16_t) * (size_t)Mf * D + sizeof(int2) * (size_t)Mf * D1);
 
   trace.point("assign + gather + neighbours");
   dev_free(slot_vid, st);

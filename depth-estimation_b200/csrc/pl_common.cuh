@@ -47,6 +47,24 @@ extern bool g_prof_on;
     PL_CUDA(cudaGetLastError());                                   \
   } while (0)
 
+// Opt-in attributes (cudaFuncSetAttribute) are per DEVICE: a process that drives several GPUs has
+// to set them once on each.  `static PerDeviceOnce once; if (once.need()) { ... }`
+struct PerDeviceOnce {
+  bool done[64] = {};
+  bool need() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+    if (done[dev]) return false;
+    done[dev] = true;
+    return true;
+  }
+};
+static inline int current_device_index() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  return dev;
+}
+
 static inline unsigned int ceil_div_u(uint64_t a, uint64_t b) { return (unsigned int)((a + b - 1) / b); }
 
 // Grid for a grid-stride kernel: enough CTAs for `items` but capped at a
@@ -65,6 +83,9 @@ struct Lattice {
   int64_t M = 0;       // vertices
   uint32_t flags = 0;
   int device = 0;
+  // stream of the most recent API call that used this lattice: pl_lattice_destroy releases the
+  // buffers in ITS order (cudaFreeAsync), so kernels still queued there finish first
+  cudaStream_t last_stream = nullptr;
   // persistent device arrays
   int32_t* vid = nullptr;    // [n][d+1] vertex id per (point, remainder)
   float* bary = nullptr;     // [n][d+1] barycentric weight per (point, remainder)

@@ -523,13 +523,18 @@ int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_re
   a.e = e; a.nblocks = nblocks; a.block_w = block_w; a.mu_rec = mu_rec; a.p = p; a.q_out = q_out;
   a.n = n; a.ntiles = (n + kTile - 1) / kTile; a.L = L; a.N = N; a.scale = scale;
   a.ring = ring_slots(N);
+#ifdef PL_DEBUG_KNOBS
+  // timing experiments only (builds with -DPL_DEBUG_KNOBS): every bit but 128 skips work and
+  // CORRUPTS the result, so the release library does not read the variable at all
   a.debug = getenv("PL_CTC_DEBUG") ? atoi(getenv("PL_CTC_DEBUG")) : 0;
+#else
+  a.debug = 0;
+#endif
   const size_t smem = ctc_smem(N);
-  static bool done = false;
-  if (!done) {
+  static PerDeviceOnce done;
+  if (done.need()) {
     PL_CUDA(cudaFuncSetAttribute(compat_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  210 * 1024));   // one CTA per SM; ctc_smem(N) <= 205 KB for every N
-    done = true;
   }
   const int64_t cap = PL_SM_COUNT;
   const unsigned grid = (unsigned)(a.ntiles < cap ? a.ntiles : cap);

@@ -117,15 +117,14 @@ int cost_volume(const float* im1, const float* im2, float* out, int h, int w, in
   const int PW = kTX + 2 * R, PH = kTY + 2 * R;
   const size_t smem = sizeof(float) * (size_t)kLC * PH * (PW + kTX);
   dim3 grid((w + kTX - 1) / kTX, (h + kTY - 1) / kTY, (L + kLC - 1) / kLC);
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.need()) {
     PL_CUDA(cudaFuncSetAttribute(cost_volume_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  128 * 1024));
     PL_CUDA(cudaFuncSetAttribute(cost_volume_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  128 * 1024));
     PL_CUDA(cudaFuncSetAttribute(cost_volume_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  128 * 1024));
-    attr = true;
   }
   if (criterion == 0) {
     PL_LAUNCH(cost_volume_kernel<0>, grid, kThreads, smem, st, im1, im2, out, h, w, ch, L, R);

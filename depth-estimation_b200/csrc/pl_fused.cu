@@ -225,13 +225,12 @@ int mf_fused_iteration(Lattice* L, bool first, const float* val_in, float* val_o
                        int labels, cudaStream_t st) {
   const int d1 = L->d + 1;
   const size_t smem = fused_smem(d1);
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.need()) {
     PL_CUDA(cudaFuncSetAttribute(mf_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  110 * 1024));
     PL_CUDA(cudaFuncSetAttribute(mf_fused_kernel<false>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-    attr_done = true;
   }
   const float inv_denom = 1.0f / (1 + powf(2, -L->d));
   if (first) {

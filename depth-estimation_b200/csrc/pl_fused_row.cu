@@ -461,11 +461,10 @@ __global__ void __launch_bounds__(kThreads, 1) mf_row_kernel(const RowArgs a) {
 template <int L, bool FIRST, bool ATM>
 int launch_row_impl(const RowArgs& a, cudaStream_t st) {
   using C = RCfg<L, ATM>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_set;
+  if (attr_set.need()) {
     PL_CUDA(cudaFuncSetAttribute((mf_row_kernel<L, FIRST, ATM>),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
-    attr_set = true;
   }
   const unsigned grid = (unsigned)(a.ntiles < PL_SM_COUNT ? a.ntiles : PL_SM_COUNT);
   PL_LAUNCH((mf_row_kernel<L, FIRST, ATM>), grid, kThreads, C::SMEM, st, a);

@@ -449,7 +449,8 @@ size_t tc_smem(int d1, bool lattice) {
 template <int L, int MODE, int D1T>
 int launch_tc(const MfArgs& a, cudaStream_t st) {
   const size_t smem = tc_smem<L>(a.d1, MODE != 2);
-  static size_t attr_smem = 0;
+  static size_t attr_smem_dev[64] = {};
+  size_t& attr_smem = attr_smem_dev[current_device_index()];
   if (smem > attr_smem) {
     PL_CUDA(cudaFuncSetAttribute((mf_tc_kernel<L, MODE, D1T>),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

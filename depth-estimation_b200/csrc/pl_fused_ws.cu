@@ -434,11 +434,10 @@ __global__ void __launch_bounds__(kThreads, 1) mf_ws_kernel(const WsArgs a) {
 template <int L, bool FIRST>
 int launch_ws(const WsArgs& a, cudaStream_t st) {
   using C = WCfg<L>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_set;
+  if (attr_set.need()) {
     PL_CUDA(cudaFuncSetAttribute((mf_ws_kernel<L, FIRST>),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
-    attr_set = true;
   }
   const unsigned grid = (unsigned)(a.ntiles < PL_SM_COUNT ? a.ntiles : PL_SM_COUNT);
   PL_LAUNCH((mf_ws_kernel<L, FIRST>), grid, kThreads, C::SMEM, st, a);

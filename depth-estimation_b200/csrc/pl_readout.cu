@@ -175,11 +175,10 @@ int readout_tiled(Lattice* L, const float* val, int labels, float denom, const f
   int G = 1;
   while (G < 32 && G < labels / 4) G <<= 1;
   const size_t smem = sizeof(float) * (size_t)(2 * TE + ((labels + 3) & ~3)) + kStageBytes;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.need()) {
     PL_CUDA(cudaFuncSetAttribute(readout_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  100 * 1024));
-    attr_done = true;
   }
   if (smem > 100 * 1024) {
     set_last_error("readout_tiled: d + 1 = %d too large", d1);

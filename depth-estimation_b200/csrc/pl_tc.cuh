@@ -7,6 +7,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace pl {
 namespace tc {
@@ -44,12 +45,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a descriptor or byte-count mistake must not hang the GPU.  Returns false
-// on timeout (the caller records it and carries on with garbage, which the tests catch).
+// Bounded wait that FAILS LOUDLY: a descriptor or byte-count mistake must neither hang the GPU nor
+// let a kernel carry on with garbage.  2^20 fast polls, then ~2^24 polls with a 256 ns back-off
+// (several seconds: slow NVLink peers, debugger / profiler replay and heavy contention all fit),
+// then __trap(): the launch fails with a sticky CUDA error that every later API call reports
+// (PL_ERR_CUDA / a torch RuntimeError).  Never returns false; the bool keeps the call sites' shape.
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
 #pragma unroll 1
-  for (int i = 0; i < (1 << 22); i++)
+  for (int i = 0; i < (1 << 20); i++)
     if (mbar_try_wait(bar, parity)) return true;
+#pragma unroll 1
+  for (int i = 0; i < (1 << 24); i++) {
+    if (mbar_try_wait(bar, parity)) return true;
+    __nanosleep(256);
+  }
+  printf("libpl_lattice: mbarrier wait timed out (block %d, thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
+  __trap();
   return false;
 }
 

@@ -430,8 +430,10 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   if (TE <= kFastMaxTE) {
     const size_t smem = sizeof(unsigned short) * (size_t)((TE + 31) / 32) * TE;
     // static (20.5 KB) + dynamic shared memory exceeds the 48 KB default: always opt in
-    PL_CUDA(cudaFuncSetAttribute(tile_build_fast_kernel,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    static PerDeviceOnce fast_attr;
+    if (fast_attr.need())
+      PL_CUDA(cudaFuncSetAttribute(tile_build_fast_kernel,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     PL_LAUNCH(tile_build_fast_kernel, (unsigned)ntiles, kThreads, smem, st, L->vid, L->bary, L->n,
               d1, L->ent_pix, L->ent_w, L->loc, L->useg, L->tile_off, L->tile_U, counter,
               L->rec_slice, L->rec_splat);
@@ -1020,15 +1022,14 @@ int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float*
                 cudaStream_t st, const float* rowscale, int64_t rs_stride, int J) {
   const int d1 = L->d + 1;
   const size_t smem = sizeof(float) * kTile * kCW + sizeof(float4) * (size_t)kTile * d1;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.need()) {
     PL_CUDA(cudaFuncSetAttribute(splat_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  100 * 1024));
     PL_CUDA(cudaFuncSetAttribute(splat_pipe_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  100 * 1024));
     PL_CUDA(cudaFuncSetAttribute(splat_pipe_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  100 * 1024));
-    attr_done = true;
   }
   static const bool no_pipe = getenv("PL_SPLAT_NO_PIPE") != nullptr;
   if (d1 == kD1p && !no_pipe && L->M < (1 << 24)) {   // vertex id and row share one 32-bit key
@@ -1064,11 +1065,10 @@ int launch_slice(Lattice* L, const float* val, int Cc, float denom, float* dst, 
                  cudaStream_t st) {
   const int d1 = L->d + 1;
   const size_t smem = sizeof(float) * STAGE * kCW + sizeof(float2) * (size_t)kTile * d1;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.need()) {
     PL_CUDA(cudaFuncSetAttribute((slice_tiled_kernel<EXACT, STAGE, EPI>),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr_done = true;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
   PL_LAUNCH((slice_tiled_kernel<EXACT, STAGE, EPI>), grid, kThreads, smem, st, val, Cc, L->n, d1,
@@ -1125,12 +1125,11 @@ int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const flo
     L->max_U = *L->h_max_U;
   }
   const int d1 = L->d + 1;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceOnce attr_done;
+  if (attr_done.need()) {
     PL_CUDA(cudaFuncSetAttribute(slice_dot_kernel<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     PL_CUDA(cudaFuncSetAttribute(slice_dot_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     PL_CUDA(cudaFuncSetAttribute(slice_dot_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr_done = true;
   }
   dim3 grid((unsigned)L->ntiles, (unsigned)((Cc + kCW - 1) / kCW), 1);
   const size_t ent = sizeof(float2) * (size_t)kTile * d1;

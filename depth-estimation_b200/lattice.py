@@ -27,7 +27,12 @@ class PermutohedralLattice:
     for all points; ``filter`` = splat values -> blur -> slice.
     """
 
-    def __init__(self, ref, ref_grow_quirk=False):
+    def __init__(self, ref, ref_grow_quirk=True):
+        """``ref_grow_quirk`` (default on): reproduce the reference's hash-table growth behaviour
+        (permutohedral.h:59-62,101-155: the lookup that doubles the table probes from a stale
+        slot and can add a duplicate vertex), so vertex count, ids, keys, neighbours and filtered
+        values equal the reference's for every M; off = one vertex per distinct key.  The two are
+        the same lattice while M < 16383."""
         N.require_cuda_f32(ref, "ref", 2)
         ref = ref.contiguous()
         self.device = ref.device
@@ -40,7 +45,7 @@ class PermutohedralLattice:
         self.num_vertices = int(N.lib().pl_lattice_num_vertices(self._h))
 
     @classmethod
-    def from_rgb(cls, rgb, s_ij=0.1, s_rgb=0.1):
+    def from_rgb(cls, rgb, s_ij=0.1, s_rgb=0.1, ref_grow_quirk=True):
         """Lattice of ``ijrgbGuide(s_ij, s_rgb)(rgb[None])`` (crf_module.py:106-114) for one image
         ``rgb[3, h, w]``: the features are evaluated inside the elevation kernel, bit for bit
         what the module computes, and never written to memory."""
@@ -55,7 +60,8 @@ class PermutohedralLattice:
         self._h = C.c_void_p()
         with torch.cuda.device(self.device):
             N.check(N.lib().pl_lattice_create_ijrgb(
-                C.c_void_p(rgb.data_ptr()), h, w, float(s_ij), float(s_rgb), N.PL_BUILD_DEFAULT,
+                C.c_void_p(rgb.data_ptr()), h, w, float(s_ij), float(s_rgb),
+                N.PL_BUILD_REF_GROW_QUIRK if ref_grow_quirk else N.PL_BUILD_DEFAULT,
                 N.stream_ptr(self.device), C.byref(self._h)))
         self.num_vertices = int(N.lib().pl_lattice_num_vertices(self._h))
         return self
@@ -77,6 +83,7 @@ class PermutohedralLattice:
             if out.shape[1] != c or out.stride(1) != 1:
                 raise ValueError("out must be [n, C] with unit channel stride")
         ptrs, strides = [], []
+        keep = []   # row-major temporaries must outlive the launch (their storage is the operand)
         for name, t in (("sub", sub), ("add", add)):
             if t is None:
                 ptrs.append(C.c_void_p(0))
@@ -86,6 +93,7 @@ class PermutohedralLattice:
                 if t.shape[1] != c:
                     raise ValueError(f"{name} must have {c} channels")
                 t = _rowmajor(t)
+                keep.append(t)
                 ptrs.append(C.c_void_p(t.data_ptr()))
                 strides.append(t.stride(0))
         flags = (N.PL_APPLY_EXACT_SLICE if exact_slice else 0) | (N.PL_APPLY_FLAT_KERNELS if flat else 0)
@@ -94,6 +102,7 @@ class PermutohedralLattice:
                 self._h, C.c_void_p(src.data_ptr()), src.stride(0), C.c_void_p(out.data_ptr()),
                 out.stride(0), c, ptrs[0], strides[0], ptrs[1], strides[1], flags,
                 N.stream_ptr(self.device)))
+        del keep
         return out
 
     __call__ = filter

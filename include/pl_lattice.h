@@ -53,10 +53,13 @@ typedef struct pl_lattice pl_lattice; /* opaque */
 #define PL_BUILD_DEFAULT 0u
 /* Reproduce the reference's hash-table growth quirk (permutohedral.h:102-103
  * with :62: the lookup that triggers a table doubling probes from a slot
- * computed with the old capacity, which can create one orphan duplicate
- * vertex per doubling).  Off: one vertex per distinct key (the algorithm as
- * published).  The two are identical whenever the reference table never grows
- * (M < 16383). */
+ * computed with the old capacity, which can create an extra duplicate vertex
+ * per doubling; after the next doubling the duplicate is the copy lookups
+ * find).  On: vertex count, vertex ids, keys and blur neighbours equal the
+ * reference's bit for bit (replayed on the device from the clean build, see
+ * csrc/pl_build.cu section 6).  Off: one vertex per distinct key (the
+ * algorithm as published).  The two are identical whenever the reference
+ * table never grows (M < 16383).  pl_filter / pl_filter_host always use it. */
 #define PL_BUILD_REF_GROW_QUIRK 1u
 
 /* Builds the lattice for feature vectors ref_dev[n][d] (what the reference's
@@ -72,6 +75,8 @@ int pl_lattice_create(const float* ref_dev, int64_t n, int d, uint32_t flags, vo
  * rgb_planes_dev: [3][h][w] fp32 (one image of the module's NCHW input). */
 int pl_lattice_create_ijrgb(const float* rgb_planes_dev, int h, int w, float s_ij, float s_rgb,
                             uint32_t flags, void* stream, pl_lattice** out);
+/* Releases the lattice's device memory in stream order on the stream of the most recent call
+ * that used it (kernels still queued there finish first); safe right after an asynchronous call. */
 void pl_lattice_destroy(pl_lattice* lat);
 
 int64_t pl_lattice_num_points(const pl_lattice* lat);   /* n */

@@ -14,6 +14,15 @@ def pytest_configure(config):
 
 @pytest.fixture(scope="session")
 def oracle():
+    """The CPU oracle in the reference's own behaviour (hash-growth quirk included), which is
+    what the product builds by default; identical to ``oracle_clean`` while M < 16383."""
+    from oracle.lattice_oracle import Oracle
+    return Oracle(faithful=True)
+
+
+@pytest.fixture(scope="session")
+def oracle_clean():
+    """One vertex per distinct key (``PermutohedralLattice(ref, ref_grow_quirk=False)``)."""
     from oracle.lattice_oracle import Oracle
     return Oracle(faithful=False)
 

@@ -36,12 +36,12 @@ def test_faithful_oracle_is_bit_exact(oracle_faithful, reference, n, d, C, scale
 
 
 @pytest.mark.parametrize("n,d,scale", [(60000, 5, 6.0), (120000, 5, 12.0)])
-def test_faithful_oracle_reproduces_grow_quirk(oracle_faithful, oracle, reference, n, d, scale):
+def test_faithful_oracle_reproduces_grow_quirk(oracle_faithful, oracle_clean, reference, n, d, scale):
     """Past 16383 vertices the reference's table doubles and its stale-hash lookup
     (permutohedral.h:102-103,62) can add orphan duplicates; the faithful oracle
     must follow it exactly, the clean oracle must equal its distinct-key set."""
     src, ref = _rand(n, d, 2, scale, seed=3)
-    so, sr, sc = oracle_faithful.state(ref), reference.state(ref), oracle.state(ref)
+    so, sr, sc = oracle_faithful.state(ref), reference.state(ref), oracle_clean.state(ref)
     assert so.M == sr.M and np.array_equal(so.vid, sr.vid) and np.array_equal(so.keys, sr.keys)
     assert np.array_equal(so.nbr, sr.nbr)
     assert np.array_equal(_bits(oracle_faithful.filter(src, ref)), _bits(reference.filter(src, ref)))
@@ -52,12 +52,12 @@ def test_faithful_oracle_reproduces_grow_quirk(oracle_faithful, oracle, referenc
     assert np.array_equal(so.greedy, sc.greedy) and np.array_equal(so.rank, sc.rank)
 
 
-def test_clean_equals_faithful_without_growth(oracle_faithful, oracle):
+def test_clean_equals_faithful_without_growth(oracle_faithful, oracle_clean):
     img = synthetic.image(96, 128, seed=1)
     ref = synthetic.ijrgb_features(img)
     rng = np.random.default_rng(0)
     src = rng.random((ref.shape[0], 5)).astype(np.float32)
-    a, b = oracle.build(ref), oracle_faithful.build(ref)
+    a, b = oracle_clean.build(ref), oracle_faithful.build(ref)
     assert a.ngrow == 0 and a.M == b.M
     assert np.array_equal(_bits(a.apply(src)), _bits(b.apply(src)))
 
