@@ -122,3 +122,40 @@ def logits2average_depth(logits, labels=None):
     if labels is None:
         labels = torch.arange(probs.shape[1]).float()[None, :, None, None]
     return (probs * labels).sum(1)[:, None, :, :]
+
+
+# ---- stereo Module forwards (mb_stereo_crf.py:68-102,138-163), weights passed explicitly ----------
+
+def coord_conv(x, weight, bias):
+    """oil's un-vendored ``conv2d(cin, cout, coords=True)`` as tests/golden/make_golden.py and the
+    product re-create it: 3x3 same-padded convolution over [x, i, j], i / j = linspace(-1, 1)."""
+    b, _, h, w = x.shape
+    ii = torch.linspace(-1, 1, h)[None, None, :, None].expand(b, 1, h, w)
+    jj = torch.linspace(-1, 1, w)[None, None, None, :].expand(b, 1, h, w)
+    return F.conv2d(torch.cat([x, ii, jj], dim=1), weight, bias, padding=1)
+
+
+def crf_depth_refiner(logits, imgrgb, features, proj_w, proj_b, gamma, s, niters, confidence=None):
+    """mb_stereo_crf.py:74-79 (CRFdepthRefiner.forward); with ``confidence`` :93-102."""
+    guide = torch.cat((imgrgb, F.conv2d(features, proj_w, proj_b)), dim=1)
+    return logits2average_depth(crf_as_rnn(guide, logits, gamma, s, niters, confidence))
+
+
+def uncertainty_net(imgrgb, p):
+    """mb_stereo_crf.py:84-92: coord-conv / GroupNorm(4, 16) / ReLU x 2, coord-conv -> s."""
+    x = coord_conv(imgrgb, p["0__conv__weight"], p["0__conv__bias"])
+    x = F.relu(F.group_norm(x, 4, p["1__weight"], p["1__bias"]))
+    x = coord_conv(x, p["3__conv__weight"], p["3__conv__bias"])
+    x = F.relu(F.group_norm(x, 4, p["4__weight"], p["4__bias"]))
+    return coord_conv(x, p["6__conv__weight"], p["6__conv__bias"])
+
+
+def crf_depth_upsampler(disp_lowres, img_highres, gamma, s, niters):
+    """mb_stereo_crf.py:144-163 (CRFdepthUpsampler.forward)."""
+    up = F.interpolate(disp_lowres, img_highres.size()[2:], mode='bilinear', align_corners=False)
+    labels = torch.linspace(0, float(up.max()), 18).float()
+    lab4 = labels[None, :, None, None]
+    logits = -10 * (charbonneir(lab4, up, gamma * lab4.max()) * torch.exp(s))   # crf_module.py:77-79
+    confidence = (up > 1e-2).float()
+    out = crf_as_rnn(img_highres, logits, gamma, s, niters, confidence=confidence, labels=labels)
+    return logits2average_depth(out, lab4)

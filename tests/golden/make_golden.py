@@ -66,7 +66,20 @@ def import_reference():
     _stub("oil.utils.mytqdm", tqdm=lambda x, **k: x)
     _stub("oil.architectures")
     _stub("oil.architectures.parts")
-    _stub("oil.architectures.parts.blocks", conv2d=None, ConvBNrelu=None, ResBlock=None)
+    class _CoordConv(torch.nn.Module):
+        """Stand-in for oil's un-vendored ``conv2d(cin, cout, coords=True)`` (mb_stereo_crf.py:5-7,
+        :84-90): 3x3 same-padded convolution over the input plus normalised (i, j) channels.
+        The product's ``_CoordConv2d`` is the same re-creation; the golden pins everything around it."""
+        def __init__(self, cin, cout, coords=False, **k):
+            super().__init__()
+            self.conv = torch.nn.Conv2d(cin + 2, cout, kernel_size=3, padding=1)
+
+        def forward(self, x):
+            b, _, h, w = x.shape
+            ii = torch.linspace(-1, 1, h)[None, None, :, None].expand(b, 1, h, w)
+            jj = torch.linspace(-1, 1, w)[None, None, None, :].expand(b, 1, h, w)
+            return self.conv(torch.cat([x, ii, jj], dim=1))
+    _stub("oil.architectures.parts.blocks", conv2d=_CoordConv, ConvBNrelu=None, ResBlock=None)
     _stub("crf.dataloader", MBStereo14Unary=None, StereoUpsampling05=None)
     if "matplotlib" not in sys.modules:
         try:
@@ -90,11 +103,65 @@ def import_reference():
     return ref, rgm, rcm, rmb
 
 
+def stereo_modules(synthetic, rgm, rcm, rmb):
+    """mb_stereo_crf.py:62-102,138-163: the three nn.Module forwards with the lattice pairwise
+    (``CRF.W = BatchedAdjacency``, the drop-in crf_module.py:5 imports), on CPU.  The reference
+    hard-codes ``.cuda()`` for the labels (:150; crf_module.py:73): Tensor.cuda is a no-op here."""
+    g = torch.Generator().manual_seed(21)
+    torch.manual_seed(21)
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    rec = {}
+    lg = torch.randn((2, 5, 6, 7), generator=g)
+    rec.update(logits=lg.numpy(), depth=rmb.logits2average_depth(lg).numpy(),
+               depth_labels=rmb.logits2average_depth(lg, torch.linspace(0, 2, 5)[None, :, None, None]).numpy())
+
+    def state(m, prefix):
+        return {prefix + k.replace(".", "__"): v.detach().numpy() for k, v in m.state_dict().items()}
+
+    # CRFdepthRefiner: 16-channel guide (rgb + 13 projected features) -> d = 16 lattice, L = 16 labels
+    h, w, L, d_in = 14, 18, 16, 8
+    img = torch.from_numpy(synthetic.image(h, w, seed=31)).permute(2, 0, 1)[None].contiguous()
+    feats = torch.randn((1, d_in, h, w), generator=g) * 0.5
+    logits = (-torch.from_numpy(synthetic.unary(h, w, L, 31)).reshape(h, w, L)).permute(2, 0, 1)[None].contiguous()
+    with torch.no_grad():
+        m = rmb.CRFdepthRefiner(d_in=d_in, d_guide=16, niters=2, gamma=.05)
+        m.CRF.W = rgm.BatchedAdjacency(num_threads=1)
+        m.projection.weight.mul_(4.0)          # spread the projected features over a few lattice cells
+        out = m((logits, img * 8.0, feats))
+        rec.update(state(m, "refiner__"), refiner_logits=logits.numpy(), refiner_img=(img * 8.0).numpy(),
+                   refiner_feats=feats.numpy(), refiner_out=out.numpy())
+        # CRFwUncertainty: same plus the confidence map exp(-s)
+        m = rmb.CRFwUncertainty(d_in=d_in, d_guide=16, niters=2, gamma=.05)
+        m.CRF.W = rgm.BatchedAdjacency(num_threads=1)
+        m.projection.weight.mul_(4.0)
+        out, conf = m((logits, img * 8.0, feats))
+        rec.update(state(m, "uncert__"), uncert_out=out.numpy(), uncert_conf=conf.numpy())
+        # CRFdepthUpsampler: 18 linspace labels from the low-resolution disparity (:138-163)
+        h2, w2 = 24, 32
+        img2 = torch.from_numpy(synthetic.image(h2, w2, seed=33)).permute(2, 0, 1)[None].contiguous()
+        disp = torch.from_numpy((np.add.outer(np.arange(h2 // 4), 1.5 * np.arange(w2 // 4)) % 7 + 0.5)
+                                .astype(np.float32))[None, None]
+        disp[0, 0, 0, :2] = 0.0                # unknown disparities: confidence 0 (:152)
+        m = rmb.CRFdepthUpsampler(niters=2, gamma=.05)
+        m.CRF.W = rgm.BatchedAdjacency(num_threads=1)
+        out = m((disp, img2 * 10.0, None))
+        rec.update(state(m, "upsampler__"), upsampler_disp=disp.numpy(), upsampler_img=(img2 * 10.0).numpy(),
+                   upsampler_out=out.numpy())
+        # a second frame with a different max_depth through the SAME module (label-cache regression)
+        out2 = m((disp * 1.7, img2 * 10.0, None))
+        rec.update(upsampler_out2=out2.numpy())
+    np.savez_compressed(os.path.join(HERE, "stereo_wrappers.npz"), **rec)
+
+
 def main():
     synthetic = __import__("importlib").import_module("depth_estimation_b200.synthetic")
     ref, rgm, rcm, rmb = import_reference()
     torch.manual_seed(0)
     out = {}
+    if "--only-stereo" in sys.argv:
+        stereo_modules(synthetic, rgm, rcm, rmb)
+        print("stereo_wrappers.npz written")
+        return
 
     # ---- 1. lattice integer artefacts + filter on an (r,g,b,i,j)-ordered guide -------------
     h, w = 24, 32
@@ -177,13 +244,9 @@ def main():
                         Mu2=rcm.compatibility_matrix(rcm.charbonneir2, lab).numpy(),
                         ij_guide=rcm.ijGuide(0.2)(x).detach().numpy())
 
-    # ---- 6. stereo wrappers (mb_stereo_crf.py:62-79) ---------------------------------------
+    # ---- 6. stereo wrappers and Module forwards (mb_stereo_crf.py:62-102,138-163) -----------
     if rmb is not None:
-        lg = torch.randn((2, 5, 6, 7), generator=g)
-        np.savez_compressed(os.path.join(HERE, "stereo_wrappers.npz"), logits=lg.numpy(),
-                            depth=rmb.logits2average_depth(lg).numpy(),
-                            depth_labels=rmb.logits2average_depth(
-                                lg, torch.linspace(0, 2, 5)[None, :, None, None]).numpy())
+        stereo_modules(synthetic, rgm, rcm, rmb)
     # ---- 7. cost volume and fixture readers: crf/depth.py:34-53, crf/utils.py:46-109 --------
     # crf/depth.py imports cv2.ximgproc (opencv-contrib, absent) for an unrelated guided-filter
     # operator and crf/utils.py imports skimage for `grayscale`: both stubbed, neither is called.

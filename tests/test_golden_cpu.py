@@ -75,6 +75,31 @@ def test_oracle_stereo_readout_matches_reference_golden():
     np.testing.assert_allclose(O.logits2average_depth(lg, lab).numpy(), z["depth_labels"], atol=1e-6)
 
 
+def test_oracle_stereo_modules_match_reference_golden():
+    """CRFdepthRefiner / CRFwUncertainty / CRFdepthUpsampler forwards (mb_stereo_crf.py:68-102,
+    138-163) restated in oracle/crf_oracle.py against the outputs of the reference's own classes."""
+    from oracle import crf_oracle as O
+    z = _load("stereo_wrappers.npz")
+    if "refiner_out" not in z.files:
+        pytest.skip("stereo_wrappers.npz predates the Module forwards")
+    t = lambda k: torch.from_numpy(z[k])
+    g, s0 = torch.tensor(0.05), torch.tensor(0.0)
+    out = O.crf_depth_refiner(t("refiner_logits"), t("refiner_img"), t("refiner_feats"),
+                              t("refiner__projection__weight"), t("refiner__projection__bias"), g, s0, 2)
+    np.testing.assert_allclose(out.numpy(), z["refiner_out"], rtol=0, atol=2e-5)
+    un = {k[len("uncert__uncertainty_net__"):]: t(k) for k in z.files if k.startswith("uncert__uncertainty_net__")}
+    conf = torch.exp(-O.uncertainty_net(t("refiner_img"), un))
+    np.testing.assert_allclose(conf.numpy(), z["uncert_conf"], rtol=1e-5, atol=1e-6)
+    out = O.crf_depth_refiner(t("refiner_logits"), t("refiner_img"), t("refiner_feats"),
+                              t("uncert__projection__weight"), t("uncert__projection__bias"), g, s0, 2,
+                              confidence=conf)
+    np.testing.assert_allclose(out.numpy(), z["uncert_out"], rtol=0, atol=5e-5)
+    out = O.crf_depth_upsampler(t("upsampler_disp"), t("upsampler_img"), g, s0, 2)
+    np.testing.assert_allclose(out.numpy(), z["upsampler_out"], rtol=0, atol=2e-5)
+    out = O.crf_depth_upsampler(t("upsampler_disp") * 1.7, t("upsampler_img"), g, s0, 2)
+    np.testing.assert_allclose(out.numpy(), z["upsampler_out2"], rtol=0, atol=2e-5)
+
+
 def test_depth_oracle_matches_reference_cost_volume_golden():
     """oracle/depth_oracle.py against crf.depth.disparity_badness itself (AD/9, SD/5, nprod/3)."""
     from oracle import depth_oracle as D

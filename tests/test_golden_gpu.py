@@ -120,3 +120,47 @@ def test_matrix_form_and_small_pieces_vs_reference_golden(native):
     assert _rel(mb.logits2average_depth(lg).cpu(), w["depth"]) < 1e-6
     labels = torch.linspace(0, 2, 5, device="cuda")[None, :, None, None]
     assert _rel(mb.logits2average_depth(lg, labels).cpu(), w["depth_labels"]) < 1e-6
+
+
+def _load_state(module, z, prefix):
+    sd = {k[len(prefix):].replace("__", "."): torch.from_numpy(np.asarray(z[k])) for k in z.files
+          if k.startswith(prefix) and "_out" not in k}
+    missing, unexpected = module.load_state_dict(sd, strict=True)
+    assert not missing and not unexpected
+
+
+@pytest.mark.parametrize("grad", [False, True])
+def test_stereo_modules_vs_reference_golden(native, grad):
+    """CRFdepthRefiner (16-channel guide -> d = 16 lattice), CRFwUncertainty (confidence map) and
+    CRFdepthUpsampler (18 linspace labels) forwards against the outputs of the reference's own
+    classes (mb_stereo_crf.py:68-102,138-163; tests/golden/make_golden.py stereo_modules), through
+    the fused no-grad path and through the autograd path."""
+    mb = importlib.import_module("depth_estimation_b200.crf.mb_stereo_crf")
+    z = _load("stereo_wrappers.npz")
+    t = lambda k: torch.from_numpy(z[k]).cuda()
+    ctx = torch.enable_grad() if grad else torch.no_grad()
+    tol = 5e-4      # of the depth range (soft-argmax over energies that are within 2e-4)
+    with ctx:
+        m = mb.CRFdepthRefiner(d_in=8, d_guide=16, niters=2, gamma=.05)
+        _load_state(m, z, "refiner__")
+        m = m.cuda()
+        out = m((t("refiner_logits"), t("refiner_img"), t("refiner_feats")))
+        assert out.shape == z["refiner_out"].shape
+        assert _rel(out.detach().cpu(), z["refiner_out"]) < tol
+
+        m = mb.CRFwUncertainty(d_in=8, d_guide=16, niters=2, gamma=.05)
+        _load_state(m, z, "uncert__")
+        m = m.cuda()
+        torch.backends.cudnn.allow_tf32 = False
+        out, conf = m((t("refiner_logits"), t("refiner_img"), t("refiner_feats")))
+        assert _rel(conf.detach().cpu(), z["uncert_conf"]) < 1e-4
+        assert _rel(out.detach().cpu(), z["uncert_out"]) < tol
+
+        m = mb.CRFdepthUpsampler(niters=2, gamma=.05)
+        _load_state(m, z, "upsampler__")
+        m = m.cuda()
+        out = m((t("upsampler_disp"), t("upsampler_img"), None))
+        assert _rel(out.detach().cpu(), z["upsampler_out"]) < tol
+        # second frame, different max_depth, same module: the labels (and Mu) must be rebuilt
+        out2 = m((t("upsampler_disp") * 1.7, t("upsampler_img"), None))
+        assert _rel(out2.detach().cpu(), z["upsampler_out2"]) < tol
