@@ -36,7 +36,7 @@ def ref_impl(oracle_faithful):
     return Reference() if Reference.available() else oracle_faithful
 
 
-def _check(native, ref_impl, ref, src):
+def _check(native, ref_impl, ref, src, values=True):
     st = ref_impl.state(ref)
     lat = native.PermutohedralLattice(_cuda(ref))          # default: reference behaviour
     ex = {k: v.cpu().numpy() for k, v in lat.export().items()}
@@ -47,6 +47,8 @@ def _check(native, ref_impl, ref, src):
     assert np.array_equal(ex["vid"], st.vid)
     assert np.array_equal(ex["keys"], st.keys)
     assert np.array_equal(ex["nbr"], st.nbr)
+    if not values:
+        return st
     want = ref_impl.filter(src, ref)
     assert _relerr(lat.filter(_cuda(src)).cpu().numpy(), want) < TOL
     assert _relerr(native.lattice.filter(_cuda(src), _cuda(ref)).cpu().numpy(), want) < TOL
@@ -81,7 +83,12 @@ def test_random_features_match_reference(native, ref_impl, n, d, scale, seed):
 def test_doubling_inside_blur(native, ref_impl, oracle_clean, d, scale):
     """splat() ends exactly on the threshold: the table doubles at the first lookup of blur()
     (create = false, permutohedral.h:516), which then reports its neighbour absent if the stale
-    slot misses.  The input is trimmed so that its LAST lookup creates vertex 16383."""
+    slot misses.  The input is trimmed so that its LAST lookup creates vertex 16383.
+
+    Only the integer artefacts are comparable here: when grow() runs inside blur() the reference
+    goes on using the value array grow() has just freed (`hashTableBase`, permutohedral.h:490-491,
+    :519-523, :539-541 against :127-132) -- its filtered VALUES are undefined behaviour in this
+    corner (about one input in n(d+1) per doubling), so there is nothing to be equal to."""
     rng = np.random.default_rng(5)
     full = (rng.random((40000, d)) * scale).astype(np.float32)
     T = 16383
@@ -96,7 +103,7 @@ def test_doubling_inside_blur(native, ref_impl, oracle_clean, d, scale):
     else:
         pytest.skip("no alignment found")
     src = rng.standard_normal((ref.shape[0], 2)).astype(np.float32)
-    st = _check(native, ref_impl, ref, src)
+    st = _check(native, ref_impl, ref, src, values=False)
     assert st.M == T
 
 
