@@ -2,50 +2,46 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-Workload (BASELINE.json configs[1]): Middlebury quarter-res 740x500 stereo pair,
-64 disparity labels, 5-D (i, j, r, g, b) guide with s_ij = s_rgb = 0.1, charb
-compatibility, 5 mean-field iterations, synthetic data.  A step is one frame
-per rank: build the lattice from the guide features, then 5 fused iterations.
-Image-parallel over ranks, no collective on the data path (weak scaling).
+Headline workload (BASELINE.json configs[1], the largest configuration the reference's own CPU arm
+finishes in a bounded time): Middlebury quarter-res 740x500 stereo pair, 64 disparity labels, 5-D
+(i, j, r, g, b) guide with s_ij = s_rgb = 0.1, charb compatibility, 5 mean-field iterations,
+synthetic data.  A step is one frame per rank: build the lattice from the guide features, then 5
+fused iterations.  Image-parallel over ranks, no collective on the data path (weak scaling).
 
-`value`  : frames/s with features and unaries already resident in HBM.
-`e2e`    : frames/s through the module API (CRFasRNN.forward -> soft-argmax
-           depth) from pinned HOST buffers, H2D of guide+logits and D2H of the
-           depth map inside the timed region.
-`roofline`: dominant kernel's algorithmic bytes / its mean launch duration
-           (CUDA events on the launching stream, separate profiling pass right
-           after the timed steps) against the measured HBM copy bandwidth.
-`cpu_baseline`: the reference's CPU path (oracle/_ref when built, else the C
-           restatement) on this box's host cores, rank 0, N = 1 only.
+`value`    : frames/s with features and unaries already resident in HBM (K steps, L2 flushed between).
+`sustained`: the same step back to back for >= 2 s (no flush: E0 + P + E exceed L2), with its clocks.
+`e2e`      : frames/s from pinned HOST buffers through the public API, copies inside the timed region.
+             value = the stereo notebooks' whole pipeline (two images in -> cost volume -> guide ->
+             5 iterations -> soft-argmax depth out; `stereo_pair_depth`), two frames in flight;
+             `module_call` = CRFasRNN.forward -> depth with the guide and the 95 MB cost volume
+             uploaded per frame (the reference-facing module boundary), pipelined and serial.
+`roofline` : dominant kernel's algorithmic bytes / its mean launch duration (CUDA events on the
+             launching stream, separate profiling pass) against the measured HBM copy bandwidth.
+`cpu_baseline`: the reference's CPU path (oracle/_ref when built) on one host core, rank 0, N = 1.
+`extra.configs`: the other BASELINE.json configurations (bench_extra.py), each with clocks, M/n,
+             roofline on SURVEY 8d's algorithmic bytes and an extrapolated CPU baseline.
 """
 import argparse
 import importlib
 import json
 import os
-import statistics
-import subprocess
 import sys
-import tempfile
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+import bench_util as U  # noqa: E402
+
 H, W, L, NITERS, D = 500, 740, 64, 5, 5
 S_IJ = S_RGB = 0.1
 GAMMA = 0.05
 WORKLOAD = "middlebury_quarter_740x500_L64_5mf_forward"
-
-
-def _peaks():
-    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(path):
-        try:
-            return float(json.load(open(path))["hbm_gbs"]), "measured"
-        except Exception:
-            pass
-    return 6650.0, "fallback"
+# byte-identical in both arms (the driver compares them)
+CONFIG = {"workload": WORKLOAD, "h": H, "w": W, "labels": L, "mf_iters": NITERS, "d": D,
+          "s_ij": S_IJ, "s_rgb": S_RGB, "gamma": GAMMA, "l2": "flushed between timed steps (256 MiB write)"}
+METRIC = "stereo_crf_frames_per_s_5mf"
 
 
 def _inputs(seed):
@@ -58,164 +54,45 @@ def _inputs(seed):
     return np.ascontiguousarray(img), feats, e0, mu
 
 
-class _ClockSampler:
-    """SM clock and throttle reasons DURING the timed region, polled through NVML from a thread
-    (the timed region lasts tens of milliseconds: `nvidia-smi -lms` is too coarse for it)."""
-    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
-               0x4: "sw_power_cap"}
-
-    def __init__(self, gpu_index):
-        self.gpu, self.thread, self.stop_flag = gpu_index, None, False
-        self.sm, self.bits, self.max_mhz, self.power = [], 0, None, []
-
-    def _run(self):
-        try:
-            import pynvml as nv
-            nv.nvmlInit()
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            idx = self.gpu
-            if vis:
-                try:
-                    idx = int(vis.split(",")[self.gpu])
-                except Exception:
-                    idx = self.gpu
-            h = nv.nvmlDeviceGetHandleByIndex(idx)
-            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
-            while not self.stop_flag:
-                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
-                try:
-                    self.bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
-                except Exception:
-                    try:
-                        self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
-                    except Exception:
-                        pass
-                try:
-                    self.power.append(nv.nvmlDeviceGetPowerUsage(h) / 1000.0)
-                except Exception:
-                    pass
-                time.sleep(0.002)
-        except Exception:
-            pass
-
-    def start(self):
-        import threading
-        self.thread = threading.Thread(target=self._run, daemon=True)
-        self.thread.start()
-
-    def stop(self):
-        self.stop_flag = True
-        if self.thread is not None:
-            self.thread.join(timeout=5)
-        out = {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": len(self.sm)}
-        if self.sm:
-            out["sm_mhz"] = statistics.median(self.sm)
-        if self.power:
-            out["power_w_max"] = max(self.power)
-        out["reasons"] = sorted(name for bit, name in self.REASONS.items() if self.bits & bit)
-        return out
-
-
-def _algorithmic_bytes(kernel, n, M, C, launches_per_frame=None):
-    """Per-launch algorithmic HBM bytes; d = 5, fp32."""
-    d1 = D + 1
-    if kernel.startswith(("mf_ws_kernel", "mf_row_kernel", "mf_tc_kernel", "mf_fused_kernel")):
-        # fused iteration: first launch of a frame reads E0, writes P (+ splat record, lattice
-        # rows written); the others also read P_prev, the slice record and the blurred lattice.
-        first = 8 * n * C + 9 * n * d1 + 4 * M * C
-        later = 12 * n * C + 15 * n * d1 + 8 * M * C
-        k = NITERS if launches_per_frame is None else int(round(launches_per_frame))
-        return (first + (k - 1) * later) / k
-    if kernel.startswith("splat"):             # read src + entry lists, write lattice values
-        return 4 * n * C + 9 * n * d1 + 4 * M * C
-    if kernel.startswith("blur_kernel"):       # one axis: read + write values, neighbour ids
-        return 8 * M * C + 8 * M
-    if kernel.startswith("blur_"):             # all d+1 axes in one launch
-        return d1 * (8 * M * C + 8 * M)
-    if kernel.startswith("slice"):             # read values + entry lists + P + E0, write E
-        return 4 * M * C + 6 * n * d1 + 12 * n * C
-    if kernel.startswith("softmax_compat"):    # read E, write P, Mu once
-        return 8 * n * C + 4 * C * C
-    return None
-
-
-def _ncu_traffic(kernel):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, taken from the
-    committed ncu --set full summary (profiles/ncu_traffic.json); None if not captured."""
-    try:
-        tab = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        for key, val in tab.items():
-            if kernel.startswith(key):
-                return val["dram_bytes_per_launch"]
-    except Exception:
-        pass
-    return None
-
-
-def cpu_frame_seconds(backend, feats, e0, mu, iters):
-    """The reference's CPU path for `iters` mean-field iterations of one frame,
-    pixel-major: crf_module.py:97-103 with W = filter - id (gaussian_matrix.py:352);
-    the lattice is rebuilt inside every filter call, as the reference does."""
-    import numpy as np
-    import torch
-    torch.set_num_threads(1)
-    e0_t = torch.from_numpy(e0)
-    mu_t = torch.from_numpy(mu)
-    t0 = time.perf_counter()
-    e = e0_t
-    for _ in range(iters):
-        p = torch.softmax(-e, dim=1) @ mu_t.t()
-        f = torch.from_numpy(backend.filter(np.ascontiguousarray(p.numpy()), feats))
-        e = e0_t + (f - p)
-    return time.perf_counter() - t0
-
-
-def _cpu_backend():
-    from oracle.lattice_oracle import Oracle, Reference
-    if Reference.available():
-        try:
-            return Reference()
-        except Exception:
-            pass
-    return Oracle(faithful=True)
-
-
 def _ref_worker(seed):
     img, feats, e0, mu = _inputs(seed)
-    return cpu_frame_seconds(_cpu_backend(), feats, e0, mu, 1)
+    return U.cpu_frame_seconds(U.cpu_backend(), feats, e0, mu, NITERS)
 
 
 def run_reference(args, rank, world):
     """--impl reference: the reference's own CPU implementation of the path on the host cores.
     The filter is single-threaded; its only parallelism is one process per image
-    (gaussian_matrix.py:370-377), so `cores` frames run side by side.  Each step is a bounded
-    sample: ONE mean-field iteration per frame (lattice rebuilt in the call, as the reference
-    does), scaled x5 to the 5-iteration frame."""
+    (gaussian_matrix.py:370-377), so `cores` frames run side by side, each a FULL frame (5 iterations,
+    lattice rebuilt inside every filter call as the reference does).  A step = one such batch; the
+    number of timed steps is bounded so that the run ends within a few minutes."""
     if rank != 0:
         return
     import multiprocessing as mp
     cores = os.cpu_count() or 1
     procs = max(1, min(cores, 16))
-    backend = _cpu_backend()
+    backend = U.cpu_backend()
     ctx = mp.get_context("fork")
     times = []
+    budget_s, t_start = 150.0, time.perf_counter()
     with ctx.Pool(procs) as pool:
-        for step in range(args.warmup + args.steps):
-            # workers time only the CRF iteration, not the synthetic-input generation
+        for step in range(min(args.warmup, 1) + args.steps):
+            timed = step >= min(args.warmup, 1)            # one untimed batch warms the page cache
             dt = max(pool.map(_ref_worker, [1000 * step + i for i in range(procs)]))
-            if step >= args.warmup:
+            if timed:
                 times.append(dt)
-    per_step = sum(times) / len(times)           # procs frames x 1 iteration
-    frame_s = per_step * NITERS                   # scaled to 5 iterations
-    value = procs / frame_s
-    sample = (f"{procs} frames in parallel processes, 1 of {NITERS} mean-field iterations each "
-              f"(lattice rebuilt inside the filter call), time x{NITERS}")
+            if time.perf_counter() - t_start > budget_s and times:
+                break
+    per_step = sum(times) / len(times)           # procs full frames
+    value = procs / per_step
+    sample = (f"{procs} frames in parallel processes, all {NITERS} mean-field iterations each (lattice "
+              f"rebuilt inside every filter call); {len(times)} timed batches"
+              + ("" if len(times) == args.steps else f" of the {args.steps} requested (bounded to {budget_s:.0f} s)"))
     print(json.dumps({
-        "impl": "reference", "metric": "stereo_crf_frames_per_s_5mf", "value": value,
+        "impl": "reference", "metric": METRIC, "value": value,
         "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "timed_steps": len(times),
         "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "h": H, "w": W, "labels": L, "mf_iters": NITERS, "d": D},
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": CONFIG,
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": procs, "kind": backend.kind,
                          "sample": sample},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0,
@@ -244,6 +121,41 @@ def _bind_to_gpu_numa_node(local_rank):
         return None
 
 
+class _Pipelined:
+    """`nt` host threads, each with its own copy / compute streams, take alternate frames so that the
+    H2D of one frame overlaps the device work of the other.  `frame(t, copy_st, comp_st)` enqueues one
+    frame for thread t and returns when that frame's result is on the host."""
+
+    def __init__(self, dev, nt, frame):
+        import torch
+        self.dev, self.nt, self.frame = dev, nt, frame
+        self.streams = [(torch.cuda.Stream(dev), torch.cuda.Stream(dev)) for _ in range(nt)]
+
+    def run(self, steps):
+        import threading
+        import torch
+        errors = []
+
+        def worker(t, frames):
+            try:
+                torch.cuda.set_device(self.dev)
+                with torch.no_grad():
+                    for _ in range(frames):
+                        self.frame(t, *self.streams[t])
+            except Exception as exc:               # surface worker failures in the main thread
+                errors.append(exc)
+
+        share = [steps // self.nt + (1 if t < steps % self.nt else 0) for t in range(self.nt)]
+        threads = [threading.Thread(target=worker, args=(t, share[t])) for t in range(self.nt)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        torch.cuda.synchronize(self.dev)
+        if errors:
+            raise errors[0]
+
+
 def run_ours(args, rank, local_rank, world):
     import numpy as np
     import torch
@@ -256,7 +168,7 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=dev)
     import depth_estimation_b200 as pkg
     cm = importlib.import_module("depth_estimation_b200.crf.crf_module")
-    mb = importlib.import_module("depth_estimation_b200.crf.mb_stereo_crf")
+    gm = importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
     N = pkg._native
     N.lib()
 
@@ -290,7 +202,7 @@ def run_ours(args, rank, local_rank, world):
     for _ in range(args.warmup):
         step()
     barrier()
-    sampler = _ClockSampler(local_rank)
+    sampler = U.ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     launches0 = N.launch_count()
@@ -313,112 +225,98 @@ def run_ours(args, rank, local_rank, world):
 
     if args.only_step:
         if rank == 0:
-            print(json.dumps({"metric": "stereo_crf_frames_per_s_5mf", "value": value,
-                              "ms_per_step": ms_per_step, "only_step": True}))
+            print(json.dumps({"metric": METRIC, "value": value, "ms_per_step": ms_per_step, "only_step": True}))
         return
 
-    # ---- end to end through the module API from pinned host buffers ----
+    # ---- sustained: the same step back to back for >= 2 s (boost clocks of a 20 ms burst prove nothing) ----
+    sus_steps = max(args.steps, int(2200.0 / max(ms_per_step, 1e-3)) + 1)
+    barrier()
+    sampler = U.ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(sus_steps):
+        step()
+    b.record()
+    torch.cuda.synchronize(dev)
+    sus_ms = reduce_max(a.elapsed_time(b))
+    sus_clocks = sampler.stop() if rank == 0 else None
+    sustained = {"value": world * sus_steps * 1e3 / sus_ms, "unit": "frames/s", "steps": sus_steps,
+                 "seconds": sus_ms * 1e-3, "ms_per_step": sus_ms / sus_steps, "clocks": sus_clocks,
+                 "l2": "not flushed: E0, P and E of a frame (3 x 94.7 MB) exceed the 126 MB L2"}
+
+    # ---- e2e (a): the stereo pipeline, two images in -> depth map out, from pinned host buffers ----
+    NT = 2
+    left_h = torch.from_numpy(np.ascontiguousarray(img)).pin_memory()
+    right_h = torch.from_numpy(np.ascontiguousarray(np.roll(img, -5, axis=1))).pin_memory()
+    lt_d = [torch.empty_like(left_h, device=dev) for _ in range(NT)]
+    rt_d = [torch.empty_like(right_h, device=dev) for _ in range(NT)]
+    pair_out_h = [torch.empty((H, W), dtype=torch.float32).pin_memory() for _ in range(NT)]
+    evs = [torch.cuda.Event() for _ in range(NT)]
+
+    def pair_frame(t, copy_st, comp_st):
+        with torch.cuda.stream(copy_st):
+            lt_d[t].copy_(left_h, non_blocking=True)
+            rt_d[t].copy_(right_h, non_blocking=True)
+            evs[t].record(copy_st)
+        with torch.cuda.stream(comp_st):
+            comp_st.wait_event(evs[t])
+            depth = cm.stereo_pair_depth(lt_d[t], rt_d[t], niters=NITERS, gamma=GAMMA, max_disp=L,
+                                         s_ij=S_IJ, s_rgb=S_RGB)
+            pair_out_h[t].copy_(depth, non_blocking=True)
+        comp_st.synchronize()          # this frame's depth map is on the host
+
+    pair_pipe = _Pipelined(dev, NT, pair_frame)
+    pair_pipe.run(max(args.warmup, 6 * NT))
+    barrier()
+    t0 = time.perf_counter()
+    pair_pipe.run(args.steps * 4)
+    barrier()
+    pair_value = world * args.steps * 4 / reduce_max(time.perf_counter() - t0)
+    pair_serial_pipe = _Pipelined(dev, 1, pair_frame)
+    pair_serial_pipe.run(args.warmup)
+    barrier()
+    t0 = time.perf_counter()
+    pair_serial_pipe.run(args.steps * 2)
+    barrier()
+    pair_serial = world * args.steps * 2 / reduce_max(time.perf_counter() - t0)
+
+    # ---- e2e (b): the module call, guide + cost volume uploaded per frame ----
     crf = cm.CRFasRNN(cm.charb(GAMMA), niters=NITERS).to(dev)
     guide_h = torch.from_numpy(feats).reshape(H, W, D).permute(2, 0, 1)[None].contiguous().pin_memory()
     logits_h = (-torch.from_numpy(e0)).reshape(H, W, L).permute(2, 0, 1)[None].contiguous().pin_memory()
-    depth_h = torch.empty((1, 1, H, W), dtype=torch.float32).pin_memory()
-
-    def e2e_step():
-        with torch.no_grad():
-            g = guide_h.to(dev, non_blocking=True)
-            lg = logits_h.to(dev, non_blocking=True)
-            depth = crf.depth(g, lg)      # = logits2average_depth(crf(g, lg)), read-out fused
-            depth_h.copy_(depth, non_blocking=True)
-            torch.cuda.synchronize(dev)
-        gm.clear_lattice_cache()
-
-    gm = importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
-    for _ in range(args.warmup):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    e2e_serial_s = reduce_max(time.perf_counter() - t0)
-    e2e_serial = world * args.steps / e2e_serial_s
-
-    # Same work with two frames in flight: two host threads, each with its own copy / compute
-    # streams and device buffers, take alternate frames, so the H2D copy of one frame overlaps
-    # the CRF of the other (the module call blocks its thread while the lattice's vertex count
-    # comes back).  Every frame's H2D and D2H is inside the timed region.
-    import threading
-    NT = 2
-    streams = [(torch.cuda.Stream(dev), torch.cuda.Stream(dev)) for _ in range(NT)]
     g_d = [torch.empty_like(guide_h, device=dev) for _ in range(NT)]
     lg_d = [torch.empty_like(logits_h, device=dev) for _ in range(NT)]
     dh = [torch.empty((1, 1, H, W), dtype=torch.float32).pin_memory() for _ in range(NT)]
 
-    def worker(t, frames, errors):
-        try:
-            torch.cuda.set_device(dev)
-            copy_st, comp_st = streams[t]
-            ev = torch.cuda.Event()
-            with torch.no_grad():
-                for _ in range(frames):
-                    with torch.cuda.stream(copy_st):
-                        g_d[t].copy_(guide_h, non_blocking=True)
-                        lg_d[t].copy_(logits_h, non_blocking=True)
-                        ev.record(copy_st)
-                    ev.synchronize()               # inputs are on the device
-                    with torch.cuda.stream(comp_st):
-                        depth = crf.depth(g_d[t], lg_d[t])
-                        dh[t].copy_(depth, non_blocking=True)
-                    comp_st.synchronize()          # this frame's depth map is on the host
-                    gm.forget(g_d[t])
-        except Exception as exc:                   # surface worker failures in the main thread
-            errors.append(exc)
+    def module_frame(t, copy_st, comp_st):
+        with torch.cuda.stream(copy_st):
+            g_d[t].copy_(guide_h, non_blocking=True)
+            lg_d[t].copy_(logits_h, non_blocking=True)
+            evs[t].record(copy_st)
+        with torch.cuda.stream(comp_st):
+            comp_st.wait_event(evs[t])
+            depth = crf.depth(g_d[t], lg_d[t])     # = logits2average_depth(crf(g, lg)), read-out fused
+            dh[t].copy_(depth, non_blocking=True)
+        comp_st.synchronize()
+        gm.forget(g_d[t])
 
-    def e2e_pipelined(steps):
-        errors = []
-        share = [steps // NT + (1 if t < steps % NT else 0) for t in range(NT)]
-        threads = [threading.Thread(target=worker, args=(t, share[t], errors)) for t in range(NT)]
-        for th in threads:
-            th.start()
-        for th in threads:
-            th.join()
-        torch.cuda.synchronize(dev)
-        if errors:
-            raise errors[0]
-
-    e2e_pipelined(max(args.warmup, 6 * NT))   # both threads past their first-touch allocations
+    mod_pipe = _Pipelined(dev, NT, module_frame)
+    mod_pipe.run(max(args.warmup, 6 * NT))
     barrier()
     t0 = time.perf_counter()
-    e2e_pipelined(args.steps)
+    mod_pipe.run(args.steps)
     barrier()
-    e2e_s = reduce_max(time.perf_counter() - t0)
-    e2e_value = world * args.steps / e2e_s
+    mod_value = world * args.steps / reduce_max(time.perf_counter() - t0)
+    mod_serial_pipe = _Pipelined(dev, 1, module_frame)
+    mod_serial_pipe.run(args.warmup)
+    barrier()
+    t0 = time.perf_counter()
+    mod_serial_pipe.run(args.steps)
+    barrier()
+    mod_serial = world * args.steps / reduce_max(time.perf_counter() - t0)
     gm.clear_lattice_cache()
-
-    # ---- extra: the stereo notebooks' whole pipeline, two images in -> depth map out ----
-    # (cost volume crf/depth.py:34-53 with max_disp = L, guide fused into the lattice build,
-    # 5 mean-field iterations, soft-argmax fused into the last slice; H2D of both images and
-    # D2H of the depth map inside the timed region)
-    left_h = torch.from_numpy(np.ascontiguousarray(img)).pin_memory()
-    right_h = torch.from_numpy(np.ascontiguousarray(np.roll(img, -5, axis=1))).pin_memory()
-    pair_depth_h = torch.empty((H, W), dtype=torch.float32).pin_memory()
-
-    def pair_step():
-        with torch.no_grad():
-            lt = left_h.to(dev, non_blocking=True)
-            rt = right_h.to(dev, non_blocking=True)
-            pair_depth_h.copy_(cm.stereo_pair_depth(lt, rt, niters=NITERS, gamma=GAMMA, max_disp=L),
-                               non_blocking=True)
-            torch.cuda.synchronize(dev)
-
-    for _ in range(args.warmup):
-        pair_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        pair_step()
-    barrier()
-    pair_value = world * args.steps / reduce_max(time.perf_counter() - t0)
 
     # ---- per-kernel durations for the roofline (separate pass, same inputs) ----
     roofline = None
@@ -430,59 +328,81 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.synchronize(dev)
         N.profile(False)
         rep = N.profile_report()
-        peak, how = _peaks()
+        peak, how = U.peaks()
         M = state["M"]
-        top = max(rep.items(), key=lambda kv: kv[1][1])
-        name, (cnt, ms) = top
-        nbytes = _algorithmic_bytes(name, n, M, L, cnt / 3)
+        name, (cnt, ms) = max(rep.items(), key=lambda kv: kv[1][1])
+        nbytes = U.kernel_bytes(name, n, M, L, NITERS, cnt / 3)
         frame_ms = sum(v[1] for v in rep.values()) / 3
         kernels = {k: {"launches_per_frame": v[0] / 3, "ms_per_frame": v[1] / 3,
                        "share": v[1] / 3 / frame_ms} for k, v in rep.items()}
+        fb = U.bytes_frame(n, M, L, NITERS)
+        roofline = {"bound": "hbm", "kernel": name, "achieved": None, "peak": peak, "unit": "GB/s",
+                    "frac": None, "traffic": U.ncu_traffic(name), "peak_source": how,
+                    "vertices": M, "M_over_n": M / n, "kernels": kernels,
+                    "frame": {"algorithmic_bytes": fb, "achieved": fb / (ms_per_step * 1e-3) / 1e9,
+                              "frac": fb / (ms_per_step * 1e-3) / 1e9 / peak,
+                              "scope": "B_build + 5 B_iter (SURVEY 8d) over ms_per_step"}}
         if nbytes is not None:
             achieved = nbytes / (ms / cnt * 1e-3) / 1e9
-            roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak,
-                        "unit": "GB/s", "frac": achieved / peak, "traffic": _ncu_traffic(name),
-                        "peak_source": how, "avg_launch_us": ms / cnt * 1e3,
-                        "algorithmic_bytes_per_launch": nbytes, "vertices": M, "kernels": kernels}
-        else:
-            roofline = {"bound": "hbm", "kernel": name, "achieved": None, "peak": peak,
-                        "unit": "GB/s", "frac": None, "traffic": None, "peak_source": how,
-                        "kernels": kernels}
+            roofline.update({"achieved": achieved, "frac": achieved / peak, "avg_launch_us": ms / cnt * 1e3,
+                             "algorithmic_bytes_per_launch": nbytes})
 
     # ---- CPU baseline: rank 0, N = 1 only ----
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        backend = _cpu_backend()
-        secs = cpu_frame_seconds(backend, feats, e0, mu, NITERS)
+        backend = U.cpu_backend()
+        secs = U.cpu_frame_seconds(backend, feats, e0, mu, NITERS)
         cpu = {"value": 1.0 / secs, "unit": "frames/s", "cores": 1, "kind": backend.kind,
                "sample": f"1 full frame ({NITERS} iterations, lattice rebuilt per filter call), "
                          f"single thread, {secs:.2f} s"}
 
+    # ---- the other BASELINE configurations ----
+    extra_cfgs, extra_err = None, None
+    if not args.no_extra:
+        try:
+            import bench_extra as X
+            del feats_d, e0_d
+            torch.cuda.empty_cache()
+            if world == 1:
+                extra_cfgs = X.single_gpu_extras(pkg, dev, local_rank, flush,
+                                                 with_cpu=not args.no_cpu_baseline, quick=args.quick)
+            elif hasattr(X, "multi_gpu_extras"):
+                extra_cfgs = X.multi_gpu_extras(pkg, dev, rank, local_rank, world)
+        except Exception:
+            import traceback
+            extra_err = traceback.format_exc()[-1500:]
+
     if rank == 0:
         print(json.dumps({
-            "metric": "stereo_crf_frames_per_s_5mf", "value": value, "unit": "frames/s",
+            "metric": METRIC, "value": value, "unit": "frames/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "h": H, "w": W, "labels": L, "mf_iters": NITERS,
-                       "d": D, "frames_per_step_per_gpu": 1, "parallelism": f"image-parallel x{world}", "rank0_numa_node": numa,
-                       "l2": "flushed between timed steps (256 MiB write)",
-                       "step": "lattice build + 5 fused mean-field iterations, inputs in HBM"},
-            "e2e": {"value": e2e_value, "unit": "frames/s",
-                    "h2d_bytes_per_step": int(guide_h.numel() + logits_h.numel()) * 4,
-                    "d2h_bytes_per_step": int(depth_h.numel()) * 4,
-                    "mode": "two frames in flight (two host threads, own streams): H2D of one overlaps the CRF of the other",
-                    "serial_value": e2e_serial},
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": CONFIG,
+            "notes": {"step": "lattice build + 5 fused mean-field iterations, inputs in HBM",
+                      "frames_per_step_per_gpu": 1, "parallelism": f"image-parallel x{world}",
+                      "rank0_numa_node": numa,
+                      "lattice": "reference-faithful build (PL_BUILD_REF_GROW_QUIRK, the Python default)"},
+            "sustained": sustained,
+            "e2e": {"value": pair_value, "unit": "frames/s",
+                    "h2d_bytes_per_step": int(2 * left_h.numel() * 4),
+                    "d2h_bytes_per_step": int(pair_out_h[0].numel()) * 4,
+                    "api": "crf_module.stereo_pair_depth(left, right): cost volume (crf/depth.py:34-53) -> guide "
+                           "fused into the lattice build -> 5 mean-field iterations -> soft-argmax fused into "
+                           "the last slice; pinned host images in, pinned host depth map out",
+                    "mode": "two frames in flight (two host threads, own copy / compute streams)",
+                    "serial_value": pair_serial,
+                    "module_call": {"value": mod_value, "serial_value": mod_serial, "unit": "frames/s",
+                                    "api": "CRFasRNN.depth(guide, logits) = logits2average_depth(CRFasRNN.forward)",
+                                    "h2d_bytes_per_step": int(guide_h.numel() + logits_h.numel()) * 4,
+                                    "d2h_bytes_per_step": int(dh[0].numel()) * 4,
+                                    "mode": "two frames in flight; PCIe-bound (102 MB per frame)"}},
             "gpu_launches": int(launches) * world,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "extra": {"lattice_filter_mpix_labels_per_s_incl_build": n * L * NITERS / (ms_per_step * 1e-3) / 1e6,
-                      "vertices": state["M"],
-                      "stereo_pair_to_depth_frames_per_s": pair_value,
-                      "stereo_pair_h2d_bytes_per_step": int(2 * left_h.numel() * 4),
-                      "stereo_pair_note": "images -> pl_cost_volume -> fused guide + 5 mean-field "
-                                          "iterations -> fused soft-argmax; one frame at a time"},
+                      "vertices": state["M"], "configs": extra_cfgs, "configs_error": extra_err},
         }))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
@@ -493,6 +413,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the other BASELINE configurations")
+    ap.add_argument("--quick", action="store_true", help="smaller set of extra configurations")
     ap.add_argument("--only-step", action="store_true",
                     help="run warm-up + timed device-resident steps only (for ncu)")
     args = ap.parse_args()
