@@ -46,6 +46,8 @@ _SIGNATURES = {
                                  C.c_void_p]),
     "pl_softmax_compat": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                     C.c_int, C.c_float, C.c_void_p]),
+    "pl_softmax_compat_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                            C.c_int, C.c_float, C.c_void_p]),
     "pl_softmax_compat_ex": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                        C.c_int, C.c_float, C.c_uint32, C.c_void_p]),
     "pl_softmax_compat_blocked": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64,

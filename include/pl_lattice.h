@@ -190,6 +190,19 @@ int pl_peer_open(const void* ipc_handle, void** dev_ptr_out);
 int pl_peer_close(void* dev_ptr);
 int pl_peer_free(void* dev_ptr);
 
+/* pl_softmax_compat for callers that cannot allocate: code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc.  (No counterpart in the reference.)
+ * Same arguments, same result; L in {16, 32, 64} only.  The scratch the
+ * transform needs (the compatibility matrix split into TF32 hi / lo operand planes, 33 280 bytes at
+ * L = 64) lives in a file-scope `static __device__` array inside the library, which every GPU that
+ * loads the library holds until the process exits; the call performs no cudaMalloc / cudaFree /
+ * pool allocation of any kind.  L > PL_NOALLOC_MAX_LABELS is rejected with PL_ERR_INVALID.
+ * All calls share that one array per device (it keeps the last call's contents; each call rewrites
+ * all of it before use, in stream order): calls that OVERLAP on the GPU race -- serialise them. */
+#define PL_NOALLOC_MAX_LABELS 64
+int pl_softmax_compat_noalloc(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
+                              int64_t n, int L, float scale, void* stream);
+
 /* Whole inference loop of CRFasRNN.forward (crf_module.py:93-104) with
  * W = lattice adjacency (gaussian_matrix.py:341-352), pixel-major:
  *   E = E0; repeat niters: P = scale * Mu softmax(-E); E = E0 + filter(P) - P
