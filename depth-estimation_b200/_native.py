@@ -54,6 +54,8 @@ _SIGNATURES = {
                                             C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
     "pl_softmax_compat_peers": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p,
                                           C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
+    "pl_softmax_compat_shards": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, C.c_void_p,
+                                           C.c_int64, C.c_int64, C.c_int, C.c_float, C.c_void_p]),
     "pl_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]),
     "pl_peer_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "pl_peer_close": (C.c_int, [C.c_void_p]),

@@ -300,7 +300,7 @@ int pl_filter_host(const float* src_host, const float* ref_host, float* dst_host
 
 static int compat_large(const float* e, int nblocks, const float* muT, float* p, float* q_out,
                         int64_t n, int L, int l0, int N, float scale, cudaStream_t st,
-                        const float* const* block_ptrs = nullptr);
+                        const float* const* block_ptrs = nullptr, float* const* out_block_ptrs = nullptr);
 
 int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev, float* q_out_dev,
                          int64_t n, int L, float scale, uint32_t flags, void* stream) {
@@ -327,12 +327,13 @@ int pl_softmax_compat_ex(const float* e_dev, const float* muT_dev, float* p_dev,
 
 static int compat_large(const float* e, int nblocks, const float* muT, float* p, float* q_out,
                         int64_t n, int L, int l0, int N, float scale, cudaStream_t st,
-                        const float* const* block_ptrs) {
+                        const float* const* block_ptrs, float* const* out_block_ptrs) {
   uint8_t* rec = nullptr;
   PL_TRY(pl::dev_alloc((void**)&rec, pl::compat_tc_mu_bytes(L, N), st));
   int r = pl::compat_tc_prepare_mu(muT, L, l0, N, rec, st);
   if (r == PL_OK)
-    r = pl::compat_tc_run(e, nblocks, L / nblocks, rec, p, q_out, n, L, N, scale, st, block_ptrs);
+    r = pl::compat_tc_run(e, nblocks, L / nblocks, rec, p, q_out, n, L, N, scale, st, block_ptrs,
+                          out_block_ptrs);
   pl::dev_free(rec, st);
   return r;
 }
@@ -371,6 +372,33 @@ int pl_softmax_compat_peers(const float* const* e_block_ptrs, int nblocks, const
   PL_TRY(pl::check_device());
   return compat_large(e_block_ptrs[0], nblocks, muT_dev, p_dev, nullptr, n, L, l0, N, scale,
                       (cudaStream_t)stream, e_block_ptrs);
+}
+
+int pl_softmax_compat_shards(const float* const* e_block_ptrs, float* const* p_block_ptrs, int nblocks,
+                             const float* muT_dev, int64_t row0, int64_t nrows, int L, float scale,
+                             void* stream) {
+  if (e_block_ptrs == nullptr || p_block_ptrs == nullptr || muT_dev == nullptr || nrows < 0 || row0 < 0 ||
+      nblocks < 1 || nblocks > 16 || L <= 0 || L % nblocks != 0 ||
+      !pl::compat_tc_supported(L, L, L / nblocks)) {
+    pl::set_last_error("pl_softmax_compat_shards: unsupported arguments (L=%d, nblocks=%d)", L, nblocks);
+    return PL_ERR_INVALID;
+  }
+  if (nrows == 0) return PL_OK;
+  const int bw = L / nblocks;
+  const float* eb[16];
+  float* pb[16];
+  for (int b = 0; b < nblocks; b++) {
+    if (e_block_ptrs[b] == nullptr || p_block_ptrs[b] == nullptr ||
+        (((uintptr_t)e_block_ptrs[b] | (uintptr_t)p_block_ptrs[b]) & 15u) != 0) {
+      pl::set_last_error("pl_softmax_compat_shards: block %d is null or misaligned", b);
+      return PL_ERR_INVALID;
+    }
+    eb[b] = e_block_ptrs[b] + row0 * bw;
+    pb[b] = p_block_ptrs[b] + row0 * bw;
+  }
+  PL_TRY(pl::check_device());
+  return compat_large(eb[0], nblocks, muT_dev, nullptr, nullptr, nrows, L, 0, L, scale,
+                      (cudaStream_t)stream, eb, pb);
 }
 
 // ---- peer memory (CUDA IPC) for the label shards ------------------------------------------

@@ -183,7 +183,7 @@ size_t compat_tc_mu_bytes(int L, int N);
 int compat_tc_prepare_mu(const float* muT, int L, int l0, int N, uint8_t* mu_rec, cudaStream_t st);
 int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_rec, float* p,
                   float* q_out, int64_t n, int L, int N, float scale, cudaStream_t st,
-                  const float* const* block_ptrs = nullptr);
+                  const float* const* block_ptrs = nullptr, float* const* out_block_ptrs = nullptr);
 int ctc_timeouts();
 // mean field (pl_meanfield.cu)
 int softmax_compat(const float* e, const float* muT, float* p, float* q_out, int64_t n, int L,

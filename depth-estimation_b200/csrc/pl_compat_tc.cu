@@ -62,6 +62,11 @@ struct CArgs {
   int nblocks, block_w;
   const uint8_t* mu_rec;  // [L/8] records of rec_bytes(N)
   float* p;             // [n][N]
+  // Optional: P is written in the same blocked layout instead, output label block b (pbw labels)
+  // to pblk[b] ([n][pbw]); the pointers may be peer-GPU memory (each label owner receives its
+  // columns of this rank's pixel rows directly, pl_softmax_compat_shards)
+  float* pblk[kMaxBlocks];
+  int use_pblk, pbw;
   float* q_out;         // [n][L] plain layout, or null
   int64_t n, ntiles;
   int L, N;
@@ -292,10 +297,19 @@ __global__ void __launch_bounds__(kThreads, 1) compat_tc_kernel(const CArgs a) {
         }
         bar_epi();
         if (4 * l < cw && !(a.debug & 8)) {
+          if (a.use_pblk) {
+            const int c = c0 + 4 * l, b = c / a.pbw;
+            float* base = a.pblk[b] + (c - b * a.pbw);
 #pragma unroll 8
-          for (int r = g; r < rows; r += kEpi / 16)
-            *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
-                *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
+            for (int r = g; r < rows; r += kEpi / 16)
+              *reinterpret_cast<float4*>(base + (p0 + r) * a.pbw) =
+                  *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
+          } else {
+#pragma unroll 8
+            for (int r = g; r < rows; r += kEpi / 16)
+              *reinterpret_cast<float4*>(a.p + (p0 + r) * a.N + c0 + 4 * l) =
+                  *reinterpret_cast<const float4*>(s_p + r * kPLD + 4 * l);
+          }
         }
         bar_epi();   // staging free again
       }
@@ -507,9 +521,20 @@ int compat_tc_prepare_mu(const float* muT, int L, int l0, int N, uint8_t* mu_rec
 
 int compat_tc_run(const float* e, int nblocks, int block_w, const uint8_t* mu_rec, float* p,
                   float* q_out, int64_t n, int L, int N, float scale, cudaStream_t st,
-                  const float* const* block_ptrs) {
+                  const float* const* block_ptrs, float* const* out_block_ptrs) {
   CArgs a;
   a.use_blk = 0;
+  a.use_pblk = 0;
+  a.pbw = block_w;
+  for (int b = 0; b < kMaxBlocks; b++) a.pblk[b] = nullptr;
+  if (out_block_ptrs != nullptr) {
+    if (nblocks > kMaxBlocks || N != L) {
+      set_last_error("blocked output needs N == L and at most %d label blocks", kMaxBlocks);
+      return PL_ERR_INVALID;
+    }
+    for (int b = 0; b < nblocks; b++) a.pblk[b] = out_block_ptrs[b];
+    a.use_pblk = 1;
+  }
   for (int b = 0; b < kMaxBlocks; b++) a.blk[b] = nullptr;
   if (block_ptrs != nullptr) {
     if (nblocks > kMaxBlocks) {

@@ -180,6 +180,20 @@ int pl_softmax_compat_peers(const float* const* e_block_ptrs, int nblocks, const
                             float* p_dev, int64_t n, int L, int l0, int N, float scale,
                             void* stream);
 
+/* The pixel / label TRANSPOSE form of the sharded iteration (softmax and compatibility
+ * couple labels but not pixels, the filter couples pixels but not labels): every rank holds label
+ * block b of E and of P for ALL pixels, e_block_ptrs[b] / p_block_ptrs[b] = [n][L / nblocks], its own
+ * and -- through pl_peer_open -- its peers'.  This call does the softmax + compatibility transform of
+ * pixel rows row0 .. row0 + nrows - 1 (this rank's pixel shard) for all L labels, reading the rows
+ * from every block in place and writing the P rows straight into the owners' blocks:
+ *   P[b][p][j] = scale * sum_k Mu[b * bw + j][k] * softmax_k(-E[.][p][.])[k],   row0 <= p < row0 + nrows.
+ * Per rank and iteration n/G * L floats cross NVLink in each direction instead of the n * L floats of
+ * the all-gather form, and no rank repeats another's softmax.  L % 64 == 0, L <= 256, 16-byte aligned
+ * blocks; the caller orders the ranks around the call (E complete before, P complete after). */
+int pl_softmax_compat_shards(const float* const* e_block_ptrs, float* const* p_block_ptrs, int nblocks,
+                             const float* muT_dev, int64_t row0, int64_t nrows, int L, float scale,
+                             void* stream);
+
 /* Device buffers other processes on this node can map (CUDA IPC; one process per GPU).
  * pl_peer_alloc: cudaMalloc + export handle (PL_IPC_HANDLE_BYTES opaque bytes to send to the peers).
  * pl_peer_open : map a peer's buffer into this process (not valid in the exporting process).
