@@ -28,6 +28,11 @@ class OracleBackend:
         q = torch.softmax(-e, dim=1)
         return (q @ mu_t[:, l0:l0 + count]) * scale                   # sum_k Mu[l][k] q[k]
 
+    def compat_rows(self, e_blocks, mu_t, scale):
+        world, rows, w = e_blocks.shape
+        e = e_blocks.permute(1, 0, 2).reshape(rows, world * w)
+        return (torch.softmax(-e, dim=1) @ mu_t) * scale
+
     def filter_update(self, p, e0):
         f = torch.from_numpy(self.h.apply(np.ascontiguousarray(p.numpy())))
         return e0 + (f - p)
@@ -51,7 +56,7 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, h, w, L, niters, out_dir):
+def _worker(rank, world, port, h, w, L, niters, out_dir, mode="gather"):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -60,7 +65,8 @@ def _worker(rank, world, port, h, w, L, niters, out_dir):
         e0 = synthetic.unary(h, w, L, seed=3)
         mu = synthetic.charb_matrix(L) * 0.5
         l0, cnt = ls.label_shard(L, world, rank)
-        mf = ls.LabelShardedMeanField(OracleBackend(ref))
+        cls = ls.LabelShardedMeanField if mode == "gather" else ls.TransposeExchangeMeanField
+        mf = cls(OracleBackend(ref))
         e = mf.run(torch.from_numpy(np.ascontiguousarray(e0[:, l0:l0 + cnt])), torch.from_numpy(mu),
                    niters, 1.2)
         np.save(os.path.join(out_dir, f"shard{rank}.npy"), e.numpy())
@@ -77,6 +83,27 @@ def test_label_sharded_mean_field_gloo(tmp_path, world):
     ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=3))
     want = _unsharded(ref, synthetic.unary(h, w, L, seed=3), synthetic.charb_matrix(L) * 0.5, niters, 1.2)
     assert np.abs(got - want).max() / np.abs(want).max() < 1e-5
+
+
+@pytest.mark.parametrize("world,h,w", [(2, 16, 20), (4, 16, 20), (4, 9, 14)])
+def test_transpose_exchange_mean_field_gloo(tmp_path, world, h, w):
+    """Pixel shards for softmax + compat, label shards for the filter, two all-to-alls per iteration
+    (h * w = 126 leaves the last ranks with a short / empty pixel shard)."""
+    L, niters = 8, 3
+    mp.spawn(_worker, args=(world, _free_port(), h, w, L, niters, str(tmp_path), "transpose"),
+             nprocs=world, join=True)
+    got = np.concatenate([np.load(tmp_path / f"shard{r}.npy") for r in range(world)], axis=1)
+    ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=3))
+    want = _unsharded(ref, synthetic.unary(h, w, L, seed=3), synthetic.charb_matrix(L) * 0.5, niters, 1.2)
+    assert np.abs(got - want).max() / np.abs(want).max() < 1e-5
+
+
+def test_pixel_shard_arithmetic():
+    for n, world in [(1000, 4), (126, 4), (2900000, 8), (128, 2), (1, 3)]:
+        rows = [ls.pixel_shard(n, world, r) for r in range(world)]
+        assert rows[0][0] == 0 and sum(c for _, c in rows) == n
+        for (a, ca), (b, _) in zip(rows, rows[1:]):
+            assert a + ca == b and (ca % 128 == 0 or b == n)
 
 
 def test_partition_arithmetic():
