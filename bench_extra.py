@@ -210,3 +210,136 @@ def single_gpu_extras(pkg, dev, local_rank, flush, with_cpu=True, quick=False):
             out.extend(filter_entries(pkg, dev, local_rank, flush, h, w, chans, v, cpu_models))
             torch.cuda.empty_cache()
     return out
+
+
+def multi_gpu_extras(pkg, dev, rank, local_rank, world, steps=3, warmup=2):
+    """N > 1: config 4 label-sharded over the ranks (strong scaling) in four exchange forms -- NCCL
+    all-gather (the baseline north_star names), peer-memory reads, the pixel / label transpose over NCCL
+    all-to-alls, and the transpose as one kernel over peer memory -- and config 5 image-parallel."""
+    import torch
+    import torch.distributed as dist
+    ls = importlib.import_module("depth_estimation_b200.crf.label_shards")
+    synthetic = importlib.import_module("depth_estimation_b200.synthetic")
+    out = []
+    peak, how = U.peaks()
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(step):
+        for _ in range(warmup):
+            step()
+        barrier()
+        total = 0.0
+        for _ in range(steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            a.record()
+            step()
+            b.record()
+            torch.cuda.synchronize(dev)
+            total += a.elapsed_time(b)
+        t = torch.tensor([total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    h, w, L, niters = 1450, 2000, 256, 5
+    n = h * w
+    if L % world == 0:
+        for variant in ("default", "sharp_textured"):
+            feats = torch.from_numpy(U.features(h, w, variant, seed=7)).to(dev)   # every rank the same guide
+            mu = torch.from_numpy(synthetic.charb_matrix(L, 0.05)).to(dev)
+            l0, cnt = ls.label_shard(L, world, rank)
+            g = torch.Generator(device=dev).manual_seed(100)
+            e0 = torch.randn((n, L), generator=g, device=dev).abs_().mul_(4)[:, l0:l0 + cnt].contiguous()
+            state = {}
+            for mode in ("nccl_all_gather", "peer_memory_reads", "nccl_transpose_all_to_all",
+                         "peer_memory_transpose"):
+                box = {}
+
+                def step():
+                    lat = pkg.PermutohedralLattice(feats)
+                    if mode == "nccl_all_gather":
+                        res = ls.LabelShardedMeanField(ls.CudaBackend(lat)).run(e0, mu, niters, 1.0)
+                    elif mode == "peer_memory_reads":
+                        if "b" not in box:
+                            box["b"] = ls.PeerMemoryBackend(lat, n, cnt)
+                        box["b"].lat = lat
+                        res = box["b"].run(e0, mu, niters, 1.0).clone()
+                    elif mode == "nccl_transpose_all_to_all":
+                        res = ls.TransposeExchangeMeanField(ls.CudaBackend(lat)).run(e0, mu, niters, 1.0)
+                    else:
+                        if "b" not in box:
+                            box["b"] = ls.PeerTransposeMeanField(n, cnt, dev)
+                        res = box["b"].run(lat, e0, mu, niters, 1.0)
+                    state["M"], state["out"] = lat.num_vertices, res
+                    lat.close()
+
+                ms, clocks, err = None, None, None
+                try:
+                    sampler = U.ClockSampler(local_rank).start() if rank == 0 else None
+                    ms = timed(step)
+                    clocks = sampler.stop() if sampler is not None else None
+                except Exception as exc:     # a mode that cannot run on this box is reported, not fatal
+                    err = repr(exc)[:200]
+                if "b" in box:
+                    try:
+                        box["b"].close()
+                    except Exception:
+                        pass
+                if rank == 0:
+                    M = state.get("M", 0)
+                    nb = U.bytes_frame(n, M, L, niters)
+                    per_iter = {"nccl_all_gather": 4 * n * L * (world - 1) / world,
+                                "peer_memory_reads": 4 * n * L * (world - 1) / world}.get(
+                                    mode, 2 * 4 * n * L * (world - 1) / world / world)
+                    e = {"workload": f"crf_{w}x{h}_L{L}_{niters}mf_{variant}_label_sharded",
+                         "metric": "stereo_crf_frames_per_s_5mf", "unit": "frames/s", "n_gpus": world,
+                         "scaling": "strong", "exchange": mode, "features": variant, "vertices": M,
+                         "M_over_n": M / n, "clocks": clocks,
+                         "nvlink_bytes_received_per_rank_per_iteration": per_iter}
+                    if ms is not None:
+                        e.update({"value": 1e3 / ms, "ms_per_frame": ms,
+                                  "roofline": {"bound": "hbm", "scope": "whole frame over ALL ranks' HBM",
+                                               "algorithmic_bytes": nb, "achieved": nb / (ms * 1e-3) / 1e9,
+                                               "peak": peak * world, "unit": "GB/s",
+                                               "frac": nb / (ms * 1e-3) / 1e9 / (peak * world),
+                                               "peak_source": how}})
+                    else:
+                        e["unavailable"] = err
+                    out.append(e)
+                barrier()
+            del e0, feats
+            torch.cuda.empty_cache()
+
+    # ---- config 5: 1920x1080 x 128, 8 frames per rank, no collective ----
+    h, w, L, niters, frames = 1080, 1920, 128, 5, 8
+    n = h * w
+    feats = torch.from_numpy(U.features(h, w, "default", seed=7 + rank)).to(dev)
+    mu = torch.from_numpy(synthetic.charb_matrix(L, 0.05)).to(dev)
+    g = torch.Generator(device=dev).manual_seed(200 + rank)
+    e0 = torch.randn((n, L), generator=g, device=dev).abs_().mul_(4)
+    state = {}
+
+    def step5():
+        for _ in range(frames):
+            lat = pkg.PermutohedralLattice(feats)
+            state["out"] = lat.mean_field(e0, mu, niters, 1.0)
+            state["M"] = lat.num_vertices
+            lat.close()
+
+    sampler = U.ClockSampler(local_rank).start() if rank == 0 else None
+    ms = timed(step5)
+    clocks = sampler.stop() if sampler is not None else None
+    if rank == 0:
+        M = state["M"]
+        nb = U.bytes_frame(n, M, L, niters) * frames
+        out.append({"workload": f"crf_{w}x{h}_L{L}_{niters}mf_default_batch{frames * world}_image_parallel",
+                    "metric": "stereo_crf_frames_per_s_5mf", "unit": "frames/s", "n_gpus": world,
+                    "scaling": "weak", "value": frames * world * 1e3 / ms, "ms_per_step": ms,
+                    "frames_per_gpu": frames, "vertices": M, "M_over_n": M / n, "clocks": clocks,
+                    "roofline": {"bound": "hbm", "scope": "whole frames, per GPU", "algorithmic_bytes": nb,
+                                 "achieved": nb / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                 "frac": nb / (ms * 1e-3) / 1e9 / peak, "peak_source": how}})
+    return out

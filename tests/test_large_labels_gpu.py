@@ -161,16 +161,66 @@ def test_peer_memory_backend_single_process(native):
         backend.close()
 
 
-def test_peer_shards_two_gpus(native):
-    """Two processes, two GPUs: peer-memory label sharding against the NCCL all-gather form and
-    the unsharded loop (skipped on a single-GPU box)."""
+@pytest.mark.parametrize("L,G", [(128, 2), (256, 4), (256, 8), (64, 1)])
+def test_compat_shards_emulated_on_one_gpu(native, L, G):
+    """pl_softmax_compat_shards with the G label blocks of E and P all on this GPU: each emulated rank
+    processes its pixel shard and writes the P rows into every owner's block; the assembled P equals
+    the plain transform (crf_module.py:99-102 with :71-75)."""
+    import ctypes as C
+    ls = importlib.import_module("depth_estimation_b200.crf.label_shards")
+    N = native._native
+    n, w = 1000, L // G
+    g = torch.Generator(device="cuda").manual_seed(L + G)
+    e = torch.randn((n, L), generator=g, device="cuda") * 3
+    mu = torch.from_numpy(synthetic.charb_matrix(L) * 0.6).cuda()
+    mu_t = mu.t().contiguous()
+    want = (torch.softmax(-e.double(), 1) @ mu_t.double() * 1.2).float()
+    eb = [e[:, b * w:(b + 1) * w].contiguous() for b in range(G)]
+    pb = [torch.full((n, w), float("nan"), device="cuda") for _ in range(G)]
+    ep = (C.c_void_p * G)(*[t.data_ptr() for t in eb])
+    pp = (C.c_void_p * G)(*[t.data_ptr() for t in pb])
+    for rank in range(G):
+        row0, cnt = ls.pixel_shard(n, G, rank)
+        N.check(N.lib().pl_softmax_compat_shards(ep, pp, G, C.c_void_p(mu_t.data_ptr()), row0, cnt, L,
+                                                 C.c_float(1.2), N.stream_ptr(e.device)))
+    torch.cuda.synchronize()
+    got = torch.cat(pb, dim=1)
+    assert torch.isfinite(got).all()
+    assert _rel(got, want) < 1e-5
+    assert N.lib().pl_debug_tc_timeouts() == 0
+
+
+def test_peer_transpose_single_process(native):
+    """world = 1 PeerTransposeMeanField: IPC buffers, fences and iteration order against the plain loop."""
+    ls = importlib.import_module("depth_estimation_b200.crf.label_shards")
+    h, w, L, niters = 40, 56, 128, 3
+    ref = synthetic.ijrgb_features(synthetic.image(h, w, seed=1), 0.1, 0.1)
+    e0 = torch.from_numpy(synthetic.unary(h, w, L, seed=1)).cuda()
+    mu = torch.from_numpy(synthetic.charb_matrix(L) * 0.7).cuda()
+    lat = native.PermutohedralLattice(torch.from_numpy(ref).cuda())
+    want = lat.mean_field(e0, mu, niters, 1.1)
+    pt = ls.PeerTransposeMeanField(h * w, L, e0.device)
+    try:
+        for _ in range(2):
+            assert _rel(pt.run(lat, e0, mu, niters, 1.1), want) < 2e-5
+        tr = ls.TransposeExchangeMeanField(ls.CudaBackend(lat)).run(e0, mu, niters, 1.1)
+        assert _rel(tr, want) < 2e-5
+    finally:
+        pt.close()
+
+
+def test_peer_shards_all_gpus(native):
+    """One process per GPU on every GPU of the box (2, 4 or 8): NCCL all-gather, peer-memory reads and
+    both transpose-exchange forms against the unsharded loop (skipped only on a single-GPU box)."""
     import os
     import subprocess
     import sys
-    if torch.cuda.device_count() < 2:
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
         pytest.skip("needs two GPUs")
+    world = 8 if ngpu >= 8 else (4 if ngpu >= 4 else 2)
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", "29731", os.path.join(root, "tools", "peer_check.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]

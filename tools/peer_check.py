@@ -1,5 +1,6 @@
-"""torchrun --nproc-per-node G tools/peer_check.py : peer-memory label sharding on G GPUs against
-the NCCL all-gather form and the unsharded single-GPU loop (same inputs on every rank)."""
+"""torchrun --nproc-per-node G tools/peer_check.py : label sharding on G GPUs -- NCCL all-gather,
+peer-memory reads, the pixel / label transpose exchange over NCCL all-to-alls and its one-kernel
+peer-memory form -- against the unsharded single-GPU loop (same inputs on every rank)."""
 import importlib
 import os
 import sys
@@ -38,6 +39,14 @@ def main():
         errs.append(float((got - ref_shard).abs().max()) / scale)
         errs.append(float((got - gathered).abs().max()) / scale)
     backend.close()
+    # pixel / label transpose exchange: NCCL all-to-alls, then the one-kernel peer-memory form
+    tr = ls.TransposeExchangeMeanField(ls.CudaBackend(lat)).run(shard0, mu, niters, 1.1)
+    errs.append(float((tr - want[:, l0:l0 + cnt]).abs().max()) / float(want.abs().max()))
+    pt = ls.PeerTransposeMeanField(h * w, cnt, dev)
+    for _ in range(2):
+        got = pt.run(lat, shard0, mu, niters, 1.1)
+        errs.append(float((got - want[:, l0:l0 + cnt]).abs().max()) / float(want.abs().max()))
+    pt.close()
     t = torch.tensor([max(errs)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     timeouts = pkg._native.lib().pl_debug_tc_timeouts()
