@@ -286,7 +286,7 @@ slice_kernel(const float* __restrict__ val, int Cc, const int32_t* __restrict__ 
 // (the lattice of a stereo frame is a few MB, L2 resident; 6 launches of a few microseconds
 // each were launch-bound).  Optionally zeroes the buffer that does NOT hold the result, which
 // is the next mean-field iteration's splat target.
-template <typename Idx>
+template <typename Idx, int BATCH>
 __global__ void __launch_bounds__(256)
 blur_all_kernel(float* __restrict__ buf0, float* __restrict__ buf1, const int2* __restrict__ nbr,
                 Idx M, int Cc, int D1, int zero_other) {
@@ -294,24 +294,45 @@ blur_all_kernel(float* __restrict__ buf0, float* __restrict__ buf1, const int2* 
   cg::grid_group grid = cg::this_grid();
   const Idx V = (Idx)(Cc / 4);
   const Idx total = M * V;
+  const Idx stride = (Idx)gridDim.x * blockDim.x;
   float* in = buf0;
   float* out = buf1;
   for (int j = 0; j < D1; j++) {
     const int2* nbr_j = nbr + (size_t)j * M;
-    for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-         t += (Idx)gridDim.x * blockDim.x) {
-      const Idx v = t / V;
-      const int c = (int)(t - v * V) * 4;
-      const int2 nb = nbr_j[v];
-      const float4 o = __ldcg(reinterpret_cast<const float4*>(in + (int64_t)v * Cc + c));
-      const float4 a = __ldcg(reinterpret_cast<const float4*>(in + (int64_t)nb.x * Cc + c));
-      const float4 b = __ldcg(reinterpret_cast<const float4*>(in + (int64_t)nb.y * Cc + c));
-      float4 r;
-      r.x = __fmaf_rn(0.5f, b.x, __fmaf_rn(0.5f, a.x, o.x));
-      r.y = __fmaf_rn(0.5f, b.y, __fmaf_rn(0.5f, a.y, o.y));
-      r.z = __fmaf_rn(0.5f, b.z, __fmaf_rn(0.5f, a.z, o.z));
-      r.w = __fmaf_rn(0.5f, b.w, __fmaf_rn(0.5f, a.w, o.w));
-      *reinterpret_cast<float4*>(out + (int64_t)v * Cc + c) = r;
+    // BATCH independent items per trip: their neighbour ids, then all 3 * BATCH row loads, are in
+    // flight together.  Lattices that spill out of L2 are DRAM-latency bound (ncu: issue-active 10 %,
+    // half the warp slots idle) and want the deeper batch; L2-resident ones want BATCH = 1 and more CTAs.
+    for (Idx t0 = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += stride * BATCH) {
+      int64_t off[BATCH], na[BATCH], nc[BATCH];
+      bool on[BATCH];
+#pragma unroll
+      for (int k = 0; k < BATCH; k++) {
+        const Idx t = t0 + (Idx)k * stride;
+        on[k] = t < total;
+        const Idx v = on[k] ? t / V : 0;
+        const int c = on[k] ? (int)(t - v * V) * 4 : 0;
+        const int2 nb = nbr_j[v];
+        off[k] = (int64_t)v * Cc + c;
+        na[k] = (int64_t)nb.x * Cc + c;
+        nc[k] = (int64_t)nb.y * Cc + c;
+      }
+      float4 o[BATCH], a[BATCH], b[BATCH];
+#pragma unroll
+      for (int k = 0; k < BATCH; k++) {
+        o[k] = __ldcg(reinterpret_cast<const float4*>(in + off[k]));
+        a[k] = __ldcg(reinterpret_cast<const float4*>(in + na[k]));
+        b[k] = __ldcg(reinterpret_cast<const float4*>(in + nc[k]));
+      }
+#pragma unroll
+      for (int k = 0; k < BATCH; k++) {
+        if (!on[k]) continue;
+        float4 r;
+        r.x = __fmaf_rn(0.5f, b[k].x, __fmaf_rn(0.5f, a[k].x, o[k].x));
+        r.y = __fmaf_rn(0.5f, b[k].y, __fmaf_rn(0.5f, a[k].y, o[k].y));
+        r.z = __fmaf_rn(0.5f, b[k].z, __fmaf_rn(0.5f, a[k].z, o[k].z));
+        r.w = __fmaf_rn(0.5f, b[k].w, __fmaf_rn(0.5f, a[k].w, o[k].w));
+        *reinterpret_cast<float4*>(out + off[k]) = r;
+      }
     }
     grid.sync();
     float* t2 = in;
@@ -320,8 +341,7 @@ blur_all_kernel(float* __restrict__ buf0, float* __restrict__ buf1, const int2* 
   }
   if (zero_other) {  // `in` holds the result; `out` is free
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-         t += (Idx)gridDim.x * blockDim.x)
+    for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride)
       *reinterpret_cast<float4*>(out + (int64_t)t * 4) = z;
   }
 }
@@ -492,18 +512,19 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
   const int64_t M = L->M;
   const uint64_t vtx_items = (uint64_t)M * (uint64_t)(Cc / 4);
   // one cooperative launch for all axes (all CTAs must be co-resident)
-  static int coop_ctas_per_sm = -1;
-  if (coop_ctas_per_sm < 0) {
-    int dev = 0, coop = 0, occ = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-    if (coop &&
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, blur_all_kernel<uint32_t>, 256, 0) ==
-            cudaSuccess)
-      coop_ctas_per_sm = occ > 4 ? 4 : occ;
+  static int coop_occ[64];             // per device: resident CTAs per SM (0: no cooperative launch)
+  static PerDeviceOnce coop_once;
+  const int devi = current_device_index();
+  if (coop_once.need()) {
+    int coop = 0, o1 = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, devi);
+    if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, blur_all_kernel<uint32_t, 1>, 256, 0) ==
+                    cudaSuccess)
+      coop_occ[devi] = o1 > 8 ? 8 : o1;
     else
-      coop_ctas_per_sm = 0;
+      coop_occ[devi] = 0;
   }
+  const int coop_ctas_per_sm = coop_occ[devi];
   // register-resident variant: d = 5 and at most 2 items per thread on 2 x 148 CTAs
   if (coop_ctas_per_sm > 0 && D1 == 6 && (uint64_t)(M + 1) * Cc < 0x7fffffffull &&
       vtx_items <= (uint64_t)PL_SM_COUNT * 2 * kBlurRegThreads * 2) {
@@ -523,15 +544,21 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
     return PL_OK;
   }
   if (coop_ctas_per_sm > 0 && vtx_items < 0x7fffffffull) {
-    unsigned grid = grid_for(vtx_items, 256, (unsigned)coop_ctas_per_sm);
+    // The passes are latency bound (ncu, profiles/r2b_summary.md: issue-active 10 %, half the warp
+    // slots idle at 4 CTAs per SM).  Measured on lattices of 10 MB ... 450 MB per buffer: 6 CTAs per SM
+    // while both buffers sit in L2, 8 beyond (1.69 ms against 2.16 ms with 4 at M = 438 000 x 256
+    // channels = 0.49 of the HBM peak); four items per thread and trip was never better than that.
+    const bool in_l2 = (uint64_t)(M + 1) * Cc * 8ull <= (64ull << 20);
+    const int ctas = in_l2 ? (coop_ctas_per_sm < 6 ? coop_ctas_per_sm : 6) : coop_ctas_per_sm;
+    unsigned grid = grid_for(vtx_items, 256, (unsigned)ctas);
     uint32_t M32 = (uint32_t)M;
     int zo = zero_other ? 1 : 0;
     int d1 = D1;
     const int2* nbr = L->nbr;
     void* args[] = {&cur, &nxt, &nbr, &M32, &Cc, &d1, &zo};
+    const void* fn = (const void*)blur_all_kernel<uint32_t, 1>;
     if (g_prof_on) prof_begin("blur_all_kernel", st);
-    cudaError_t e = cudaLaunchCooperativeKernel((const void*)blur_all_kernel<uint32_t>, dim3(grid),
-                                                dim3(256), args, 0, st);
+    cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(256), args, 0, st);
     if (g_prof_on) prof_end(st);
     g_launches++;
     PL_CUDA(e);

@@ -161,12 +161,12 @@ __global__ void __launch_bounds__(kThreads, 1) mf_ws_kernel(const WsArgs a) {
       if (!FIRST && t < a.ntiles) {
         U = a.tile_U[t];
         const int u = tid - 2 * kTile;
-        if (u >= 0 && u < U && U <= kStage) uv = a.useg[a.tile_off[t] + u].x;
+        if (u >= 0 && u < U && u < kStage) uv = a.useg[a.tile_off[t] + u].x;
       }
     };
     auto issue_inputs = [&](int64_t t, int U, int uv) {
       const int nrows = (int)min((int64_t)kTile, a.n - t * kTile);
-      const int Us = (!FIRST && U <= kStage) ? U : 0;
+      const int Us = FIRST ? 0 : min(U, kStage);   // the first kStage distinct rows; the rest come from L2
       if (tid == 0) {
         uint32_t bytes = (uint32_t)nrows * (L * 4) * (FIRST ? 1 : 2);
         if (!FIRST) bytes += (uint32_t)Us * (L * 4) + 6 * kTE;
@@ -210,24 +210,18 @@ __global__ void __launch_bounds__(kThreads, 1) mf_ws_kernel(const WsArgs a) {
       const uint32_t* lp = reinterpret_cast<const uint32_t*>(s_loc + r * kD1);
       const float2 w01 = wp[0], w23 = wp[1], w45 = wp[2];
       const float w[6] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y};
-      if (U <= kStage) {
+      {
+        // Rows of the tile's first kStage distinct vertices are staged in shared memory; entries of a
+        // tile with more distinct vertices than that (sharp feature scales: most tiles have 130-180)
+        // fetch just their overflow rows from L2 instead of sending the whole tile there.
         const uint32_t l01 = lp[0], l23 = lp[1], l45 = lp[2];
         const uint32_t lo[6] = {l01 & 0xFFFF, l01 >> 16, l23 & 0xFFFF, l23 >> 16, l45 & 0xFFFF, l45 >> 16};
-#pragma unroll
-        for (int j = 0; j < kD1; j++) {
-          const float4* rp = reinterpret_cast<const float4*>(s_rows + lo[j] * PI + col0);
-#pragma unroll
-          for (int c4 = 0; c4 < CPT / 4; c4++) {
-            const float4 x = rp[c4];
-            ffma2(acc[2 * c4], w[j], make_float2(x.x, x.y));
-            ffma2(acc[2 * c4 + 1], w[j], make_float2(x.z, x.w));
-          }
-        }
-      } else {
         const int32_t* vp = a.vid + (t * kTile + r) * kD1;
 #pragma unroll
         for (int j = 0; j < kD1; j++) {
-          const float4* rp = reinterpret_cast<const float4*>(a.val_in + (int64_t)vp[j] * L + col0);
+          const float4* rp = (U <= kStage || lo[j] < (uint32_t)kStage)
+                                 ? reinterpret_cast<const float4*>(s_rows + lo[j] * PI + col0)
+                                 : reinterpret_cast<const float4*>(a.val_in + (int64_t)vp[j] * L + col0);
 #pragma unroll
           for (int c4 = 0; c4 < CPT / 4; c4++) {
             const float4 x = rp[c4];

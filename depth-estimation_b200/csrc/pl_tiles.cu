@@ -828,12 +828,17 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
   const int64_t p0 = tile * kTile;
   const int rows = (int)min((int64_t)kTile, n - p0);
   const int U = tile_U[tile];
-  const bool staged = U <= STAGE;   // uniform per CTA
+  // The first STAGE distinct vertex rows of the tile are staged; entries whose vertex lies beyond
+  // that (tiles of sharp / textured feature sets have more distinct vertices than fit) read their
+  // row from L2 -- per entry, not per tile.
+  // (staging pays only while most of the tile's rows fit: far beyond STAGE the staged subset is reused
+  // too little to cover the copy, measured at 1080p x 128 on textured features)
+  const int Us = (U <= STAGE + STAGE / 2) ? min(U, STAGE) : 0;
   const float inv = 1.0f / denom;
 
-  if (staged) {
+  {
     const int2* seg = useg + tile_off[tile];
-    for (int i = tid; i < U * 16; i += kThreads) {
+    for (int i = tid; i < Us * 16; i += kThreads) {
       const int u = i >> 4, v = i & 15;
       if (4 * v < cw)
         *reinterpret_cast<float4*>(s_val + u * kCW + 4 * v) =
@@ -845,7 +850,10 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
   const int valid = rows * d1;
   for (int i = tid; i < TE; i += kThreads) {
     int ix = 0;
-    if (i < valid) ix = staged ? (int)rs_loc[i] * kCW : vid[tile * TE + i];
+    if (i < valid) {
+      const int lc = (int)rs_loc[i];
+      ix = lc < Us ? lc * kCW : -1 - vid[tile * TE + i];      // >= 0: staged row offset, < 0: vertex id
+    }
     s_ent[i] = make_float2(rs_bary[i], __int_as_float(ix));
   }
   __syncthreads();
@@ -872,11 +880,11 @@ slice_tiled_kernel(const float* __restrict__ val, int Cc, int64_t n, int d1,
       const float2 e = s_ent[r * d1 + j];
       const int ix = __float_as_int(e.y);
       float4 x0, x1;
-      if (staged) {
+      if (ix >= 0) {
         x0 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l);
         x1 = *reinterpret_cast<const float4*>(s_val + ix + 4 * l + 32);
       } else {
-        const float* q = val + (int64_t)ix * Cc + c0 + 4 * l;
+        const float* q = val + (int64_t)(-1 - ix) * Cc + c0 + 4 * l;
         x0 = on0 ? *reinterpret_cast<const float4*>(q) : zero;
         x1 = on1 ? *reinterpret_cast<const float4*>(q + 32) : zero;
       }
