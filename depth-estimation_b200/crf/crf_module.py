@@ -139,12 +139,13 @@ class _MeanFieldLoop(torch.autograd.Function):
         flat_refs = flat_guide(refs)
         mu_t = mu.detach().t().contiguous()
         s = float(scale)
-        qs = []
+        qs, ps = [], []
+        keep_p = bool(refs.requires_grad)        # the guide gradient needs the filter's source P_t again
         e_out = torch.empty_like(e0)
         for b in range(B):
             lat = lattice_for(flat_refs[b])
             e = e0[b]
-            per_iter = []
+            per_iter, per_iter_p = [], []
             for _ in range(niters):
                 p = torch.empty((n, L), dtype=torch.float32, device=dev)
                 q = torch.empty((n, L), dtype=torch.float32, device=dev)
@@ -154,8 +155,12 @@ class _MeanFieldLoop(torch.autograd.Function):
                         C.c_void_p(q.data_ptr()), n, L, s, st))
                 e = lat.filter(p, sub=p, add=e0[b])
                 per_iter.append(q)
+                if keep_p:
+                    per_iter_p.append(p)
             e_out[b].copy_(e)
             qs.append(per_iter)
+            ps.append(per_iter_p)
+        ctx.ps = ps
         ctx.qs, ctx.flat_refs, ctx.niters, ctx.shape = qs, flat_refs, niters, (B, L, H, W, d)
         ctx.save_for_backward(mu.detach(), scale.detach() if torch.is_tensor(scale) else torch.tensor(s))
         out = torch.empty((B, L, H, W), dtype=torch.float32, device=dev)
@@ -189,7 +194,8 @@ class _MeanFieldLoop(torch.autograd.Function):
             for t in range(ctx.niters - 1, -1, -1):
                 q = ctx.qs[b][t]
                 if need_ref:
-                    p = torch.mm(q, mu_c.t()).mul_(s)                  # P_t, the filter's source
+                    # P_t, the filter's source: kept by the forward (pl_softmax_compat's own output)
+                    p = ctx.ps[b][t] if ctx.ps[b] else torch.mm(q, mu_c.t()).mul_(s)
                     gr, wg = _grad_reference(lat, p, ctx.flat_refs[b], dE)
                     dref[b] += gr
                     dP = wg.sub_(dE)

@@ -444,26 +444,26 @@ __global__ void __launch_bounds__(256)
 neighbour_kernel(const unsigned long long* __restrict__ table,
                  const int32_t* __restrict__ slot_vid, const int16_t* __restrict__ vkeys,
                  uint32_t mask, int64_t M, int2* __restrict__ nbr) {
-  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < M;
-       v += (int64_t)gridDim.x * blockDim.x) {
-    int16_t key[D];
+  // one thread per (vertex, axis, side): a vertex's 2(d+1) probes run side by side instead of one
+  // after the other (the kernel is pure probe latency: 23 -> 6 us at M = 8 750)
+  constexpr int PER = 2 * (D + 1);
+  const int64_t total = M * PER;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t v = t / PER;
+    const int q = (int)(t - v * PER);
+    const int j = q >> 1, side = q & 1;
+    int16_t nk[D];
 #pragma unroll
-    for (int i = 0; i < D; i++) key[i] = vkeys[v * D + i];
-#pragma unroll 1
-    for (int j = 0; j <= D; j++) {
-      int16_t n1[D], n2[D];
-#pragma unroll
-      for (int i = 0; i < D; i++) {
-        // :505-509 (int16 arithmetic); for j == d the changed coordinate is
-        // the implicit last one, which is not part of the stored key
-        n1[i] = (int16_t)((i == j) ? key[i] - D : key[i] + 1);
-        n2[i] = (int16_t)((i == j) ? key[i] + D : key[i] - 1);
-      }
-      const int32_t a = table_find<D>(table, slot_vid, vkeys, mask, n1);
-      const int32_t b = table_find<D>(table, slot_vid, vkeys, mask, n2);
-      // absent neighbours point at row M, which the value buffers keep at zero (:518,522)
-      nbr[(int64_t)j * M + v] = make_int2(a < 0 ? (int)M : a, b < 0 ? (int)M : b);
+    for (int i = 0; i < D; i++) {
+      // :505-509 (int16 arithmetic); for j == d the changed coordinate is the implicit last one,
+      // which is not part of the stored key
+      const int16_t k = vkeys[v * D + i];
+      nk[i] = side == 0 ? (int16_t)((i == j) ? k - D : k + 1) : (int16_t)((i == j) ? k + D : k - 1);
     }
+    const int32_t a = table_find<D>(table, slot_vid, vkeys, mask, nk);
+    // absent neighbours point at row M, which the value buffers keep at zero (:518,522)
+    reinterpret_cast<int*>(nbr + (int64_t)j * M + v)[side] = a < 0 ? (int)M : a;
   }
 }
 
@@ -956,7 +956,7 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
     PL_LAUNCH((quirk_keys_kernel<D>), grid_for((uint64_t)Mf, 256, 8), 256, 0, st, vkeys_clean, first_e,
               vslot, qd, M, L->vkeys, slot_vid);
     PL_TRY(dev_alloc((void**)&L->nbr, sizeof(int2) * (size_t)Mf * D1, st));
-    PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)Mf, 256, 8), 256, 0, st, table, slot_vid,
+    PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)Mf * 2 * D1, 256, 8), 256, 0, st, table, slot_vid,
               L->vkeys, (uint32_t)(cap - 1), Mf, L->nbr);
     PL_LAUNCH((quirk_blur_trigger_kernel<D>), 1, 32, 0, st, qd, L->vkeys, Mf, L->nbr);
     dev_free(qd, st);
@@ -967,7 +967,7 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
   } else {
     L->vkeys = vkeys_clean;
     PL_TRY(dev_alloc((void**)&L->nbr, sizeof(int2) * (size_t)M * D1, st));
-    PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)M, 256, 8), 256, 0, st, table, slot_vid,
+    PL_LAUNCH((neighbour_kernel<D>), grid_for((uint64_t)M * 2 * D1, 256, 8), 256, 0, st, table, slot_vid,
               L->vkeys, (uint32_t)(cap - 1), M, L->nbr);
   }
   L->bytes += (int64_t)(sizeof(int16_t) * (size_t)Mf * D + sizeof(int2) * (size_t)Mf * D1);
