@@ -140,7 +140,7 @@ class _MeanFieldLoop(torch.autograd.Function):
         mu_t = mu.detach().t().contiguous()
         s = float(scale)
         qs, ps = [], []
-        keep_p = bool(refs.requires_grad)        # the guide gradient needs the filter's source P_t again
+        keep_p = bool(ctx.needs_input_grad[1])   # the guide gradient needs the filter's source P_t again
         e_out = torch.empty_like(e0)
         for b in range(B):
             lat = lattice_for(flat_refs[b])
