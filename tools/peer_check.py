@@ -21,7 +21,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
-    h, w, L, niters = 96, 128, 64 * world, 3
+    h, w, L, niters = 96, 128, min(64 * world, 256), 3   # the transpose forms produce all L labels per kernel: L <= 256
     ref = torch.from_numpy(synthetic.ijrgb_features(synthetic.image(h, w, seed=2), 0.1, 0.1)).to(dev)
     e0 = torch.from_numpy(synthetic.unary(h, w, L, seed=2)).to(dev)
     mu = torch.from_numpy(synthetic.charb_matrix(L) * 0.7).to(dev)
