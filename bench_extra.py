@@ -171,7 +171,7 @@ def filter_entries(pkg, dev, local_rank, flush, h, w, chans, variant, cpu_models
                          "algorithmic_bytes": nb, "achieved": nb / (t_apply * 1e-3) / 1e9, "peak": peak,
                          "unit": "GB/s", "frac": nb / (t_apply * 1e-3) / 1e9 / peak, "peak_source": how,
                          "build_frac": nb_b / (t_build * 1e-3) / 1e9 / peak,
-                         "dominant_kernel": _top_kernel(rep, n, M, C, 1, peak)},
+                         "dominant_kernel": _top_kernel(rep, n, M, C, 0, peak)},
             "kernels_ms": {k: round(v[1], 4) for k, v in sorted(rep.items(), key=lambda kv: -kv[1][1])[:6]},
             "build_kernels_ms": {k: round(v[1], 4)
                                  for k, v in sorted(rep_b.items(), key=lambda kv: -kv[1][1])[:9]},

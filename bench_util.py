@@ -163,8 +163,8 @@ def kernel_bytes(kernel, n, M, C, niters, launches_per_frame=None):
         return d1 * (8 * M * C + 8 * M)
     if kernel.startswith("slice_kernel"):
         return 4 * M * C + 8 * n * d1 + 4 * n * C
-    if kernel.startswith("slice"):
-        return 4 * M * C + 6 * n * d1 + 12 * n * C
+    if kernel.startswith("slice"):     # with the E0 + (KP - P) epilogue inside a CRF frame, plain in a filter
+        return 4 * M * C + 6 * n * d1 + (12 if niters > 0 else 4) * n * C
     if kernel.startswith(("softmax_compat", "compat_tc")):
         return 8 * n * C + 4 * C * C
     return None
