@@ -109,6 +109,7 @@ struct Lattice {
   // largest distinct-vertex count of a tile: reduced on the device after the tile build, copied
   // to a pinned slot, read (after the event) by the first tiled slice to size its staging buffer
   int max_U = -1;
+  int mean_U = 0;              // mean distinct-vertex count per tile (same read-back)
   int* h_max_U = nullptr;
   cudaEvent_t max_U_ev = nullptr;
   // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats

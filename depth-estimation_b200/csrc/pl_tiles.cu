@@ -389,11 +389,12 @@ int* pinned_slot() {
       ring = nullptr;
     }
   });
-  return ring == nullptr ? nullptr : ring + (next.fetch_add(1, std::memory_order_relaxed) % kSlots);
+  // two ints per lattice: {sum of U over the tiles, max U}
+  return ring == nullptr ? nullptr : ring + (next.fetch_add(2, std::memory_order_relaxed) % kSlots);
 }
 
 int tiles_max_u(Lattice* L, cudaStream_t st) {
-  int* d_max = L->tile_off + 2 * L->ntiles + 1;
+  int* d_max = L->tile_off + 2 * L->ntiles;     // {useg cursor = sum of U, max U}
   L->max_U = -1;
   L->h_max_U = pinned_slot();
   if (L->h_max_U == nullptr) {
@@ -401,7 +402,7 @@ int tiles_max_u(Lattice* L, cudaStream_t st) {
     L->max_U = 1 << 30;   // unknown: largest staging buffer
     return PL_OK;
   }
-  PL_CUDA(cudaMemcpyAsync(L->h_max_U, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+  PL_CUDA(cudaMemcpyAsync(L->h_max_U, d_max, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
   if (L->max_U_ev == nullptr) PL_CUDA(cudaEventCreateWithFlags(&L->max_U_ev, cudaEventDisableTiming));
   PL_CUDA(cudaEventRecord(L->max_U_ev, st));
   return PL_OK;
@@ -1091,7 +1092,8 @@ int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, i
                 bool exact, cudaStream_t st) {
   if (L->max_U < 0) {   // first tiled slice on this lattice: the tile build has long finished
     PL_CUDA(cudaEventSynchronize(L->max_U_ev));
-    L->max_U = *L->h_max_U;
+    L->max_U = L->h_max_U[1];
+    L->mean_U = L->ntiles > 0 ? (int)((uint32_t)L->h_max_U[0] / (uint64_t)L->ntiles) : 0;
   }
 #define PL_SLICE(EX, ST)                                                                         \
   return (sub != nullptr || add != nullptr)                                                      \
@@ -1099,12 +1101,16 @@ int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, i
                                           add, add_stride, st)                                   \
              : launch_slice<EX, ST, false>(L, val, Cc, denom, dst, dst_stride, sub, sub_stride,  \
                                            add, add_stride, st)
+  // Feature sets with little locality inside a tile (textured images at sharp scales: 350 distinct
+  // vertices per 768 entries) never stage (U > 1.5 x STAGE): the small instance leaves the shared memory
+  // to two more CTAs per SM, which is what the L2-latency-bound gathers want (ncu, profiles/r2_summary.md)
+  const bool no_locality = L->mean_U > 240;
   if (exact) {
-    if (L->max_U <= 48) PL_SLICE(true, 48);
+    if (L->max_U <= 48 || no_locality) PL_SLICE(true, 48);
     if (L->max_U <= 96) PL_SLICE(true, 96);
     PL_SLICE(true, 160);
   }
-  if (L->max_U <= 48) PL_SLICE(false, 48);
+  if (L->max_U <= 48 || no_locality) PL_SLICE(false, 48);
   if (L->max_U <= 96) PL_SLICE(false, 96);
   PL_SLICE(false, 160);
 #undef PL_SLICE
@@ -1130,7 +1136,8 @@ int slice_dot_tiled(Lattice* L, const float* val, int Cc, float denom, const flo
                     int J) {
   if (L->max_U < 0) {
     PL_CUDA(cudaEventSynchronize(L->max_U_ev));
-    L->max_U = *L->h_max_U;
+    L->max_U = L->h_max_U[1];
+    L->mean_U = L->ntiles > 0 ? (int)((uint32_t)L->h_max_U[0] / (uint64_t)L->ntiles) : 0;
   }
   const int d1 = L->d + 1;
   static PerDeviceOnce attr_done;
