@@ -150,7 +150,7 @@ def kernel_bytes(kernel, n, M, C, niters, launches_per_frame=None):
     """Per-launch algorithmic bytes of one of OUR kernels, for the dominant-kernel
     roofline.  None: no formula for this kernel."""
     d1 = D + 1
-    if kernel.startswith(("mf_ws_kernel", "mf_row_kernel", "mf_tc_kernel", "mf_fused_kernel", "mf_big")):
+    if kernel.startswith(("mf_ws_kernel", "mf_tc_kernel", "mf_fused_kernel", "mf_big")):
         first = 8 * n * C + 9 * n * d1 + 4 * M * C
         later = 12 * n * C + 15 * n * d1 + 8 * M * C
         k = niters if launches_per_frame is None else max(1, int(round(launches_per_frame)))

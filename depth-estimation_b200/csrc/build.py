@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 OUT = os.path.join(PKG, "libpl_lattice.so")
-SOURCES = ["pl_api.cu", "pl_build.cu", "pl_filter.cu", "pl_meanfield.cu", "pl_tiles.cu", "pl_fused.cu", "pl_fused_tc.cu", "pl_fused_row.cu", "pl_fused_ws.cu", "pl_cost.cu", "pl_readout.cu", "pl_compat_tc.cu", "pl_backward.cu", "pl_noalloc.cu"]
+SOURCES = ["pl_api.cu", "pl_build.cu", "pl_filter.cu", "pl_meanfield.cu", "pl_tiles.cu", "pl_fused.cu", "pl_fused_tc.cu", "pl_fused_ws.cu", "pl_cost.cu", "pl_readout.cu", "pl_compat_tc.cu", "pl_backward.cu", "pl_noalloc.cu"]
 HEADERS = ["pl_common.cuh", "pl_tc.cuh", os.path.join("..", "..", "include", "pl_lattice.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -476,10 +476,10 @@ static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT
   const bool fusable = aligned && !(flags & (PL_APPLY_FLAT_KERNELS | PL_APPLY_EXACT_SLICE |
                                              PL_MEANFIELD_UNFUSED));
   const bool use_tc = fusable && !(flags & PL_MEANFIELD_NO_TENSOR) && pl::mf_tc_supported(Lt, L);
-  // row-per-thread form (pl_fused_row.cu) where it exists, unless the caller asks for the tile form
+  // warp-specialised form (pl_fused_ws.cu; L in {32, 64}, d = 5) unless the caller asks for the tile form
   static const bool env_tile = getenv("PL_MEANFIELD_TILE_KERNEL") != nullptr;   // A/B timing knob
-  const bool use_row = use_tc && !env_tile && !(flags & PL_MEANFIELD_TILE_KERNEL) &&
-                       pl::mf_row_supported(Lt, L);
+  const bool use_ws = use_tc && !env_tile && !(flags & PL_MEANFIELD_TILE_KERNEL) &&
+                      pl::mf_ws_supported(Lt, L);
   if (use_tc || (fusable && pl::mf_fused_supported(Lt, L))) {
     // One kernel per iteration (pl_fused_tc.cu on the tensor cores, pl_fused.cu on the CUDA
     // cores): P lives in work_dev and is updated in place (a tile reads its own rows of
@@ -498,15 +498,9 @@ static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT
       // the splat target: zeroed above (first iteration) or by the previous blur
       float* target = (res == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
       float* other = (target == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
-      // warp-specialised form (pl_fused_ws.cu) by default; PL_MEANFIELD_NO_WS=1 (A/B knob)
-      // falls back to the single-group row form (pl_fused_row.cu)
-      static const bool env_no_ws = getenv("PL_MEANFIELD_NO_WS") != nullptr;
-      if (use_row && !env_no_ws && pl::mf_ws_supported(Lt, L)) {
+      if (use_ws) {
         PL_TRY(pl::mf_ws_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
                                    scale, L, st));
-      } else if (use_row) {
-        PL_TRY(pl::mf_row_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
-                                    scale, L, st));
       } else if (use_tc) {
         PL_TRY(pl::mf_tc_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
                                    scale, L, st));
@@ -671,7 +665,7 @@ int pl_profile_report(char* buf, int cap) {
 }
 
 uint64_t pl_launch_count(void) { return pl::g_launches; }
-int pl_debug_tc_timeouts(void) { return pl::tc_timeouts() + pl::ctc_timeouts() + pl::row_timeouts() + pl::ws_timeouts(); }
+int pl_debug_tc_timeouts(void) { return pl::tc_timeouts() + pl::ctc_timeouts() + pl::ws_timeouts(); }
 int pl_version(void) { return PL_VERSION; }
 
 const char* pl_error_string(int code) {

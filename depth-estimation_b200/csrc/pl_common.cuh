@@ -165,12 +165,6 @@ int mf_tc_iteration(Lattice* L, bool first, const float* val_in, float* val_out,
 int softmax_compat_tc(const float* e, const float* mu_canon, float* p, float* q_out, int64_t n,
                       int labels, float scale, cudaStream_t st);
 int tc_timeouts();
-// the same iteration, row-per-thread form, one CTA per SM (pl_fused_row.cu), L in {32, 64}, d = 5
-bool mf_row_supported(const Lattice* L, int labels);
-int mf_row_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
-                     const float* p_prev, float* p_next, const float* mu_canon, float scale,
-                     int labels, cudaStream_t st);
-int row_timeouts();
 // the same iteration, warp-specialised: main group (slice / softmax / MMA / epilogue) and splat
 // group hand the P tile over through shared memory (pl_fused_ws.cu), L in {32, 64}, d = 5
 bool mf_ws_supported(const Lattice* L, int labels);

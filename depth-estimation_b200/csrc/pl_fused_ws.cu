@@ -1,7 +1,8 @@
 // pl_fused_ws.cu -- mean-field iteration, warp-specialised form (sm_100a).  L in {32, 64}, d = 5.
 //
-// Same arithmetic and tile layout as pl_fused_row.cu, but the two shared-memory-bound gather
-// phases of a tile no longer run back to back on the same warps.  One CTA per SM, 768 threads
+// A thread of the main group owns L/4 consecutive labels of ONE pixel through slice, softmax, operand
+// split and epilogue (the TMEM lane <-> row mapping of tcgen05.ld / st is the same one); the two
+// shared-memory-bound gather phases of a tile (slice, splat) run on different warp groups.  One CTA per SM, 768 threads
 // (the two groups carry about the same number of instructions per warp):
 //
 //   main group  (warps 0-15, 128 rows x 4 column quarters, a thread owns L/4 labels of one pixel)

@@ -100,7 +100,7 @@ int64_t pl_lattice_device_bytes(const pl_lattice* lat); /* persistent device mem
  * (fp32 FMA, k ascending) instead of the tcgen05 3xTF32 path used for L in {16, 32, 64}. */
 #define PL_MEANFIELD_NO_TENSOR 8u
 /* pl_meanfield: use the tile form of the tcgen05 iteration kernel (pl_fused_tc.cu, two CTAs per
- * SM) even where the row-per-thread form (pl_fused_row.cu; L in {32, 64}, d = 5) exists. */
+ * SM) even where the warp-specialised form (pl_fused_ws.cu; L in {32, 64}, d = 5) exists. */
 #define PL_MEANFIELD_TILE_KERNEL 16u
 
 /* dst[p][c] = filter(src)[p][c] - (sub ? sub[p][c] : 0) + (add ? add[p][c] : 0)
