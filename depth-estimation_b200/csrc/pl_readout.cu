@@ -108,6 +108,71 @@ readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
   __syncthreads();
 
   const int g = tid / G, l = tid % G, groups = kThreads / G;
+  if (V <= 4 * G) {
+    // A lane owns at most four float4 of its pixel's energies: keep them in registers and reduce in
+    // two passes (group minimum, then one exp per element and two sums) -- the online form below costs
+    // an exp and a branch per element plus five shuffles and two exps per merge step.
+    for (int r = g; r < rows; r += groups) {
+      const int64_t px = p0 + r;
+      float en[16];
+      float best = INFINITY;
+      int arg = 0x7fffffff;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int v = l + k * G;
+        if (v < V) {
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int j = 0; j < d1; j++) {
+            const float w = s_w[r * d1 + j];
+            const int ix = s_idx[r * d1 + j];
+            const float4 x = staged ? *reinterpret_cast<const float4*>(s_val + ix * L + 4 * v)
+                                    : *reinterpret_cast<const float4*>(val + (int64_t)ix * L + 4 * v);
+            acc.x = __fmaf_rn(w, x.x, acc.x);
+            acc.y = __fmaf_rn(w, x.y, acc.y);
+            acc.z = __fmaf_rn(w, x.z, acc.z);
+            acc.w = __fmaf_rn(w, x.w, acc.w);
+          }
+          const float4 pp = *reinterpret_cast<const float4*>(p + px * L + 4 * v);
+          const float4 ee = *reinterpret_cast<const float4*>(e0 + px * L + 4 * v);
+          en[4 * k] = __fadd_rn(ee.x, __fsub_rn(acc.x, pp.x));
+          en[4 * k + 1] = __fadd_rn(ee.y, __fsub_rn(acc.y, pp.y));
+          en[4 * k + 2] = __fadd_rn(ee.z, __fsub_rn(acc.z, pp.z));
+          en[4 * k + 3] = __fadd_rn(ee.w, __fsub_rn(acc.w, pp.w));
+#pragma unroll
+          for (int c = 0; c < 4; c++)     // ascending label index: the first minimum wins
+            if (en[4 * k + c] < best) { best = en[4 * k + c]; arg = 4 * v + c; }
+        } else {
+          en[4 * k] = en[4 * k + 1] = en[4 * k + 2] = en[4 * k + 3] = INFINITY;
+        }
+      }
+      for (int o = G >> 1; o > 0; o >>= 1) {
+        const float b = __shfl_xor_sync(0xffffffffu, best, o, G);
+        const int a = __shfl_xor_sync(0xffffffffu, arg, o, G);
+        if (b < best || (b == best && a < arg)) { best = b; arg = a; }
+      }
+      float sum = 0.f, tsum = 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int v = l + k * G;
+        if (v < V) {
+          const float4 lb = *reinterpret_cast<const float4*>(s_lab + 4 * v);
+          const float q0 = __expf(best - en[4 * k]), q1 = __expf(best - en[4 * k + 1]);
+          const float q2 = __expf(best - en[4 * k + 2]), q3 = __expf(best - en[4 * k + 3]);
+          sum += (q0 + q1) + (q2 + q3);
+          tsum = fmaf(q0, lb.x, fmaf(q1, lb.y, fmaf(q2, lb.z, fmaf(q3, lb.w, tsum))));
+        }
+      }
+      for (int o = G >> 1; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o, G);
+        tsum += __shfl_xor_sync(0xffffffffu, tsum, o, G);
+      }
+      if (l == 0) {
+        if (depth) depth[px] = tsum / sum;
+        if (label_out) label_out[px] = arg;
+      }
+    }
+    return;
+  }
   for (int r = g; r < rows; r += groups) {
     const int64_t px = p0 + r;
     Red red;
