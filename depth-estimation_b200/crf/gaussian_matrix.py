@@ -40,6 +40,7 @@ latticefilter = _lattice.filter  # gaussian_matrix.py:16
 # that revisit many guides (e.g. several Laplacians side by side).
 _CACHE = {}
 _CACHE_MAX = 8
+_CACHE_LOCK = __import__("threading").RLock()   # callers may drive several streams from several threads
 
 
 def _key(t):
@@ -48,16 +49,18 @@ def _key(t):
 
 def _cached(t, build):
     key = _key(t)
-    hit = _CACHE.pop(key, None)
-    if hit is not None:
-        _CACHE[key] = hit                      # most recently used goes last
-        return hit[1]
-    while len(_CACHE) >= _CACHE_MAX:
-        old = _CACHE.pop(next(iter(_CACHE)))[1]
-        if isinstance(old, PermutohedralLattice):
-            old.close()
-    value = build()
-    _CACHE[key] = (t, value)
+    with _CACHE_LOCK:
+        hit = _CACHE.pop(key, None)
+        if hit is not None:
+            _CACHE[key] = hit                      # most recently used goes last
+            return hit[1]
+        while len(_CACHE) >= _CACHE_MAX:
+            old = _CACHE.pop(next(iter(_CACHE)))[1]
+            if isinstance(old, PermutohedralLattice):
+                old.close()
+    value = build()                                # outside the lock: a build waits for the device
+    with _CACHE_LOCK:
+        _CACHE[key] = (t, value)
     return value
 
 
@@ -107,13 +110,15 @@ def forget(guide_imgs):
     """Drop (and free) what the cache holds for one guide batch ``[B, d, h, w]``: its flattened
     copy and the lattices built from it.  For streaming callers: call once the frame's work
     has been enqueued (the lattice's memory is released in stream order)."""
-    hit = _CACHE.pop(_key(guide_imgs), None)
+    with _CACHE_LOCK:
+        hit = _CACHE.pop(_key(guide_imgs), None)
     if hit is None:
         return
     flat_refs = hit[1]
     if isinstance(flat_refs, torch.Tensor) and flat_refs.dim() == 3:
         for b in range(flat_refs.shape[0]):
-            lat = _CACHE.pop(_key(flat_refs[b]), None)
+            with _CACHE_LOCK:
+                lat = _CACHE.pop(_key(flat_refs[b]), None)
             if lat is not None and isinstance(lat[1], PermutohedralLattice):
                 lat[1].close()
 

@@ -75,7 +75,7 @@ readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
                      const int* __restrict__ tile_off, const int* __restrict__ tile_U,
                      float inv_denom, const float* __restrict__ p, const float* __restrict__ e0,
                      const float* __restrict__ labels, float* __restrict__ depth,
-                     int* __restrict__ label_out, int G) {
+                     int* __restrict__ label_out, int G, int stage_bytes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int TE = kTile * d1;
   float* s_w = reinterpret_cast<float*>(smem_raw);          // [TE]
@@ -89,7 +89,7 @@ readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
   const int rows = (int)min((int64_t)kTile, n - p0);
   const int U = tile_U[tile];
   const int V = L >> 2;
-  const bool staged = (size_t)U * L * 4 <= (size_t)kStageBytes;
+  const bool staged = (size_t)U * L * 4 <= (size_t)stage_bytes;
 
   if (staged) {
     const int2* seg = useg + tile_off[tile];
@@ -239,7 +239,16 @@ int readout_tiled(Lattice* L, const float* val, int labels, float denom, const f
   const int TE = kTile * d1;
   int G = 1;
   while (G < 32 && G < labels / 4) G <<= 1;
-  const size_t smem = sizeof(float) * (size_t)(2 * TE + ((labels + 3) & ~3)) + kStageBytes;
+  // staging sized by the lattice's largest tile (at most kStageBytes): the kernel is latency bound, and
+  // a 740x500 default-scale lattice needs 32 KB, not 64 -- 5 CTAs per SM instead of 3
+  if (L->max_U < 0 && L->max_U_ev != nullptr) {
+    PL_CUDA(cudaEventSynchronize(L->max_U_ev));
+    L->max_U = L->h_max_U[1];
+    L->mean_U = L->ntiles > 0 ? (int)((uint32_t)L->h_max_U[0] / (uint64_t)L->ntiles) : 0;
+  }
+  size_t stage = kStageBytes;
+  if (L->max_U > 0 && (size_t)L->max_U * labels * 4 < stage) stage = ((size_t)L->max_U * labels * 4 + 1023) & ~(size_t)1023;
+  const size_t smem = sizeof(float) * (size_t)(2 * TE + ((labels + 3) & ~3)) + stage;
   static PerDeviceOnce attr_done;
   if (attr_done.need()) {
     PL_CUDA(cudaFuncSetAttribute(readout_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -251,7 +260,7 @@ int readout_tiled(Lattice* L, const float* val, int labels, float denom, const f
   }
   PL_LAUNCH(readout_tiled_kernel, (unsigned)L->ntiles, kThreads, smem, st, val, labels, L->n, d1,
             L->loc, L->bary, L->vid, L->useg, L->tile_off, L->tile_U, 1.0f / denom, p, e0,
-            label_values, depth, label_out, G);
+            label_values, depth, label_out, G, (int)stage);
   return PL_OK;
 }
 
