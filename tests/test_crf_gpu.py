@@ -299,3 +299,46 @@ def test_fused_iteration_matches_unfused_and_oracle(native, oracle, h, w, L, nit
     for got in (fused, unfused, flat, cuda_core, tile):
         assert np.abs(got - e).max() / scale < 2e-4
         assert (got.argmin(1) == e.argmin(1)).mean() > 0.999
+
+
+def test_guide_gradient_survives_an_earlier_no_grad_call_on_the_same_tensor(native):
+    """The lattice cache holds only detached values: an inference call on a guide tensor must not
+    make a later training call on the SAME tensor lose its guide gradient (the cache used
+    to hand back the grad-less flattened copy), for the fused autograd op and for the composed path
+    through BatchedAdjacency / LatticeFilter alike."""
+    cm = importlib.import_module("depth_estimation_b200.crf.crf_module")
+    gm = importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
+    rgb, logits = _scene(24, 32, 8, seed=3)
+    guide = cm.ijrgbGuide(0.1, 0.1, trainable=False)(rgb.cuda()).clone().requires_grad_()   # a leaf that wants grad
+    lg = logits.cuda()
+    for fused in (True, False):
+        gm.clear_lattice_cache()
+        crf = cm.CRFasRNN(cm.charb(0.05), niters=2, fused=fused).cuda()
+        with torch.no_grad():
+            ref_out = crf(guide, lg)                      # fills the cache without autograd
+        guide.grad = None
+        out = crf(guide, lg)
+        assert _rel(out, ref_out) < 2e-4
+        out.square().mean().backward()
+        assert guide.grad is not None and torch.isfinite(guide.grad).all()
+        assert float(guide.grad.abs().max()) > 0
+        g_cached = guide.grad.clone()
+        # same call with a cold cache gives the same gradient
+        gm.clear_lattice_cache()
+        guide.grad = None
+        crf(guide, lg).square().mean().backward()
+        assert _rel(g_cached, guide.grad) < 1e-3
+
+
+def test_scalar_confidence_is_applied_with_autograd_on(native):
+    """CRFasRNN.depth with a python-scalar confidence: the unfused (autograd) branch used to drop it."""
+    cm = importlib.import_module("depth_estimation_b200.crf.crf_module")
+    rgb, logits = _scene(24, 32, 8, seed=4)
+    guide = cm.ijrgbGuide(0.1, 0.1, trainable=False)(rgb.cuda())
+    crf = cm.CRFasRNN(cm.charb(0.05), niters=2).cuda()
+    with torch.no_grad():
+        want = crf.depth(guide, logits.cuda(), confidence=0.5)
+    lg = logits.cuda().requires_grad_()
+    got = crf.depth(guide, lg, confidence=0.5)
+    assert _rel(got, want) < 1e-3
+    assert _rel(got, crf.depth(guide, lg)) > 1e-3          # and it is not the confidence = 1 result
