@@ -181,7 +181,9 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
                        int* __restrict__ counter, uint8_t* __restrict__ rec_slice,
                        uint8_t* __restrict__ rec_splat) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  unsigned short* s_cnt = reinterpret_cast<unsigned short*>(smem_raw);  // [nchunks][TE]
+  // per-(32-entry chunk, vertex) counts, <= 32 each: bytes (18 KB instead of 37 KB as 16-bit prefix sums,
+  // 5 CTAs per SM instead of 3); an entry adds up the counts of the chunks before its own when it scatters
+  unsigned char* s_cnt = smem_raw;                                      // [nchunks][TE]
   __shared__ int h_key[kHashSlots];
   __shared__ unsigned short h_lidx[kHashSlots];
   __shared__ int s_uvid[kFastMaxTE];
@@ -282,18 +284,14 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
       my_u[q] = u;
       my_r[q] = __popc(peers & ((1u << lane) - 1u));
       const int chunk = wid + q * (kThreads / 32);
-      if (u != 0xFFFF && my_r[q] == 0) s_cnt[chunk * TE + u] = (unsigned short)__popc(peers);
+      if (u != 0xFFFF && my_r[q] == 0) s_cnt[chunk * TE + u] = (unsigned char)__popc(peers);
     }
   }
   __syncthreads();
-  // prefix over the chunks, per vertex
+  // entries per vertex
   for (int u = tid; u < U; u += kThreads) {
     int running = 0;
-    for (int c = 0; c < nchunks; c++) {
-      const int t = s_cnt[c * TE + u];
-      s_cnt[c * TE + u] = (unsigned short)running;
-      running += t;
-    }
+    for (int c = 0; c < nchunks; c++) running += s_cnt[c * TE + u];
     s_total[u] = (unsigned short)running;
   }
   __syncthreads();
@@ -342,7 +340,9 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
       if (my_vid[q] >= 0) {
         const int u = my_u[q];
         const int chunk = wid + q * (kThreads / 32);
-        const int pos = (int)s_start[u] + (int)s_cnt[chunk * TE + u] + my_r[q];
+        int before = 0;                               // entries of this vertex in earlier chunks
+        for (int c = 0; c < chunk; c++) before += s_cnt[c * TE + u];
+        const int pos = (int)s_start[u] + before + my_r[q];
         const uint8_t pix = (uint8_t)(e / d1);
         ent_pix[e0 + pos] = pix;
         ent_w[e0 + pos] = my_w[q];
@@ -429,8 +429,8 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   L->bytes += (int64_t)(E_pad * (1 + 4 + 2 + 8 + 6 + 9) + sizeof(int) * (size_t)(2 * ntiles + 1));
   PL_CUDA(cudaMemsetAsync(counter, 0, 2 * sizeof(int), st));   // useg cursor, max U
   if (TE <= kFastMaxTE) {
-    const size_t smem = sizeof(unsigned short) * (size_t)((TE + 31) / 32) * TE;
-    // static (20.5 KB) + dynamic shared memory exceeds the 48 KB default: always opt in
+    const size_t smem = ((size_t)((TE + 31) / 32) * TE + 15) & ~(size_t)15;
+    // static (20.5 KB) + dynamic shared memory may exceed the 48 KB default: always opt in
     static PerDeviceOnce fast_attr;
     if (fast_attr.need())
       PL_CUDA(cudaFuncSetAttribute(tile_build_fast_kernel,
