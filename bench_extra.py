@@ -187,6 +187,58 @@ def filter_entries(pkg, dev, local_rank, flush, h, w, chans, variant, cpu_models
     return out
 
 
+def train_entries(pkg, dev, local_rank, steps=5):
+    """BASELINE config 2 as the reference trains it: CRFasRNN forward + backward through the autograd
+    operators (LatticeFilter.backward, gaussian_matrix.py:441-468) at 740x500 x 64, 5 iterations;
+    gradients wrt the logits, gamma, s and -- `guide_trainable` -- the guide scales s_ij, s_rgb."""
+    import torch
+    cm = importlib.import_module("depth_estimation_b200.crf.crf_module")
+    gm = importlib.import_module("depth_estimation_b200.crf.gaussian_matrix")
+    synthetic = importlib.import_module("depth_estimation_b200.synthetic")
+    h, w, L, niters = 500, 740, 64, 5
+    img = torch.from_numpy(synthetic.image(h, w, 0)).permute(2, 0, 1)[None].contiguous().to(dev)
+    logits0 = (-torch.from_numpy(synthetic.unary(h, w, L, 0))).reshape(h, w, L).permute(2, 0, 1)[None]
+    logits0 = logits0.contiguous().to(dev)
+    target = torch.from_numpy(synthetic.disparity(h, w, L, 0)).float()[None, None].to(dev)
+    labels = torch.arange(L, dtype=torch.float32, device=dev)
+    out = []
+    for name, train_guide in (("guide_trainable", True), ("guide_frozen", False)):
+        guide_mod = cm.ijrgbGuide(0.1, 0.1, trainable=train_guide).to(dev)
+        crf = cm.CRFasRNN(cm.charb(0.05), niters=niters).to(dev)
+
+        def step():
+            lg = logits0.clone().requires_grad_()
+            res = crf(guide_mod(img), lg)
+            depth = (torch.softmax(res, dim=1) * labels[None, :, None, None]).sum(1)[:, None]
+            (depth - target).abs().mean().backward()
+            gm.clear_lattice_cache()
+
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize(dev)
+        sampler = U.ClockSampler(local_rank).start()
+        ms = []
+        for _ in range(steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            step()
+            b.record()
+            torch.cuda.synchronize(dev)
+            ms.append(a.elapsed_time(b))
+        t_end = time.perf_counter() + 0.2
+        while time.perf_counter() < t_end:
+            step()
+        torch.cuda.synchronize(dev)
+        clocks = sampler.stop()
+        ms.sort()
+        med = ms[len(ms) // 2]
+        out.append({"workload": f"crf_train_{w}x{h}_L{L}_{niters}mf_{name}", "metric": "stereo_crf_train_steps_per_s",
+                    "unit": "steps/s", "value": 1e3 / med, "train_step_ms": med, "h": h, "w": w, "labels": L,
+                    "mf_iters": niters, "features": "default", "vertices": None, "M_over_n": None,
+                    "grads": "logits, gamma, s" + (", s_ij, s_rgb" if train_guide else ""), "clocks": clocks})
+    return out
+
+
 def single_gpu_extras(pkg, dev, local_rank, flush, with_cpu=True, quick=False):
     """All N = 1 entries.  ~40 s of GPU work, ~25 s of bounded CPU samples."""
     import torch
@@ -209,6 +261,8 @@ def single_gpu_extras(pkg, dev, local_rank, flush, with_cpu=True, quick=False):
         for v in ("default", "sharp", "sharp_textured"):
             out.extend(filter_entries(pkg, dev, local_rank, flush, h, w, chans, v, cpu_models))
             torch.cuda.empty_cache()
+    out.extend(train_entries(pkg, dev, local_rank))
+    torch.cuda.empty_cache()
     return out
 
 

@@ -45,7 +45,10 @@ print("| per-frame shares | " + ", ".join(f"{k.split('<')[0]} {v['share'] * 100:
 
 print("\n| workload | features | M/n | ours 1×B200 | roofline frac (SURVEY 8d bytes) | dominant kernel (its frac) | reference CPU, 1 core (extrapolated) | SM MHz |")
 print("|---|---|---|---|---|---|---|---|")
+train = [c for c in (r["extra"]["configs"] or []) if "train_step_ms" in c]
 for c in r["extra"]["configs"] or []:
+    if "train_step_ms" in c:
+        continue
     dk = c["roofline"].get("dominant_kernel") or {}
     val = (f"{c['value']:.1f} frames/s ({c['ms_per_frame']:.2f} ms)" if c["unit"] == "frames/s"
            else f"{c['value'] / 1e3:.1f} Gpix·labels/s apply ({c['ms_apply']:.3f} ms), {c['value_incl_build'] / 1e3:.1f} incl. build ({c['ms_build']:.2f} ms)")
@@ -55,6 +58,9 @@ for c in r["extra"]["configs"] or []:
     print(f"| {name} | {c['features']} | {c['M_over_n']:.3f} | {val} | {c['roofline']['frac']:.3f} | "
           f"{dk.get('kernel', '').split('<')[0]} ({dk.get('frac', 0) or 0:.2f}) | {cpuv} | {c['clocks']['sm_mhz']:.0f} |")
 
+if train:
+    print("\nTraining step (config 2: 740×500 × 64, 5 iterations, forward + backward): " + "; ".join(
+        f"{c['train_step_ms']:.2f} ms with grads wrt {c['grads']} ({c['clocks']['sm_mhz']:.0f} MHz)" for c in train) + ".")
 print("\n| GPUs | image-parallel 740×500×64: device frames/s (×1 GPU) | e2e frames/s (×) | 1080p × 128 batch, frames/s | config 4 label-sharded, ms/frame: all-gather / peer reads / transpose a2a / transpose peer kernel |")
 print("|---|---|---|---|---|")
 base_v, base_e = r["value"], r["e2e"]["value"]
