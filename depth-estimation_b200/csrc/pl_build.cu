@@ -182,11 +182,25 @@ elevate_kernel(const float* __restrict__ ref, const GuideSrc gs, int64_t n, Scal
     }
     b[0] = __fadd_rn(b[0], __fadd_rn(1.0f, b[D + 1]));
 
+    if (D1 % 2 == 0) {
+      // packed stores (d = 5: three 4-byte, three 2-byte and three 8-byte stores per point instead of
+      // eighteen scalar ones; p * D1 elements keep every pointer naturally aligned for even D1)
+      uint32_t* g32 = reinterpret_cast<uint32_t*>(greedy_out + p * D1);
+      uint16_t* r16 = reinterpret_cast<uint16_t*>(rank_out + p * D1);
+      float2* b2 = reinterpret_cast<float2*>(bary_out + p * D1);
 #pragma unroll
-    for (int i = 0; i < D1; i++) {
-      greedy_out[p * D1 + i] = (int16_t)gr[i];
-      rank_out[p * D1 + i] = (int8_t)rk[i];
-      bary_out[p * D1 + i] = b[i];
+      for (int i = 0; i < D1 / 2; i++) {
+        g32[i] = (uint32_t)(uint16_t)(int16_t)gr[2 * i] | ((uint32_t)(uint16_t)(int16_t)gr[2 * i + 1] << 16);
+        r16[i] = (uint16_t)((uint8_t)(int8_t)rk[2 * i] | ((uint16_t)(uint8_t)(int8_t)rk[2 * i + 1] << 8));
+        b2[i] = make_float2(b[2 * i], b[2 * i + 1]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < D1; i++) {
+        greedy_out[p * D1 + i] = (int16_t)gr[i];
+        rank_out[p * D1 + i] = (int8_t)rk[i];
+        bary_out[p * D1 + i] = b[i];
+      }
     }
   }
 }
@@ -540,7 +554,6 @@ __device__ __forceinline__ uint32_t count_below(const uint32_t* a, uint32_t n, u
 template <int D>
 __global__ void __launch_bounds__(1024)
 grow_replay_kernel(const int32_t* __restrict__ vid, const uint32_t* __restrict__ first_e,
-                   const int16_t* __restrict__ greedy, const int8_t* __restrict__ rank,
                    const int16_t* __restrict__ vkeys, uint32_t E, uint32_t M, GrowQuirk* out) {
   __shared__ GrowQuirk q;
   __shared__ unsigned long long cap;
@@ -595,7 +608,6 @@ grow_replay_kernel(const int32_t* __restrict__ vid, const uint32_t* __restrict__
       const uint32_t last_clean = c > 0 ? first_e[c - 1] : 0u;
       const uint32_t last_extra = j > 0 ? q.extra_entry[j - 1] : 0u;
       if (j < m && c > 0 && !(last_clean < q.extra_entry[j])) continue;   // next extra would be inside
-      if (j < m && c == 0 && j > 0) { /* only extras: fine */ }
       if (j > 0 && c < M && !(last_extra < first_e[c])) continue;        // next clean would be inside
       if (c == 0 && j == 0) continue;
       return c > 0 && (j == 0 || last_clean > last_extra) ? last_clean : last_extra;
@@ -939,8 +951,8 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
   if (quirk) {
     GrowQuirk* qd = nullptr;
     PL_TRY(dev_alloc((void**)&qd, sizeof(GrowQuirk), st));
-    PL_LAUNCH((grow_replay_kernel<D>), 1, 1024, 0, st, L->vid, first_e, L->greedy, L->rank,
-              vkeys_clean, (uint32_t)E, (uint32_t)M, qd);
+    PL_LAUNCH((grow_replay_kernel<D>), 1, 1024, 0, st, L->vid, first_e, vkeys_clean, (uint32_t)E,
+              (uint32_t)M, qd);
     int qres[1] = {0};
     int qerr = 0;
     PL_CUDA(cudaMemcpyAsync(qres, &qd->n_extras, sizeof(int), cudaMemcpyDeviceToHost, st));
