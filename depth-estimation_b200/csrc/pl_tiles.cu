@@ -183,7 +183,7 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // per-(32-entry chunk, vertex) counts, <= 32 each: bytes (18 KB instead of 37 KB as 16-bit prefix sums,
   // 5 CTAs per SM instead of 3); an entry adds up the counts of the chunks before its own when it scatters
-  unsigned char* s_cnt = smem_raw;                                      // [nchunks][TE]
+  unsigned char* s_cnt = smem_raw;                                      // [TE][4 * NW]: a vertex's chunk counts are contiguous
   __shared__ int h_key[kHashSlots];
   __shared__ unsigned short h_lidx[kHashSlots];
   __shared__ int s_uvid[kFastMaxTE];
@@ -269,7 +269,9 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
     }
   }
   const int nchunks = (TE + 31) / 32;
-  for (int i = tid; i < nchunks * U; i += kThreads) s_cnt[(i / U) * TE + (i % U)] = 0;
+  const int NW = (nchunks + 3) / 4;            // 32-bit words of counts per vertex (6 for d = 5)
+  uint32_t* s_cnt32 = reinterpret_cast<uint32_t*>(s_cnt);
+  for (int i = tid; i < U * NW; i += kThreads) s_cnt32[i] = 0u;
   __syncthreads();
 
   // 3. in-chunk stable rank + per-(chunk, vertex) counts
@@ -284,14 +286,14 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
       my_u[q] = u;
       my_r[q] = __popc(peers & ((1u << lane) - 1u));
       const int chunk = wid + q * (kThreads / 32);
-      if (u != 0xFFFF && my_r[q] == 0) s_cnt[chunk * TE + u] = (unsigned char)__popc(peers);
+      if (u != 0xFFFF && my_r[q] == 0) s_cnt[u * (4 * NW) + chunk] = (unsigned char)__popc(peers);
     }
   }
   __syncthreads();
   // entries per vertex
   for (int u = tid; u < U; u += kThreads) {
-    int running = 0;
-    for (int c = 0; c < nchunks; c++) running += s_cnt[c * TE + u];
+    unsigned running = 0;
+    for (int wd = 0; wd < NW; wd++) running += __vsadu4(s_cnt32[u * NW + wd], 0u);   // sum of the four bytes
     s_total[u] = (unsigned short)running;
   }
   __syncthreads();
@@ -340,9 +342,14 @@ tile_build_fast_kernel(const int32_t* __restrict__ vid, const float* __restrict_
       if (my_vid[q] >= 0) {
         const int u = my_u[q];
         const int chunk = wid + q * (kThreads / 32);
-        int before = 0;                               // entries of this vertex in earlier chunks
-        for (int c = 0; c < chunk; c++) before += s_cnt[c * TE + u];
-        const int pos = (int)s_start[u] + before + my_r[q];
+        unsigned before = 0;                          // entries of this vertex in earlier chunks
+        for (int wd = 0; wd < NW; wd++) {
+          const int nb = chunk - 4 * wd;              // bytes of this word that belong to earlier chunks
+          if (nb <= 0) break;
+          const uint32_t m = nb >= 4 ? 0xFFFFFFFFu : ((1u << (8 * nb)) - 1u);
+          before += __vsadu4(s_cnt32[u * NW + wd] & m, 0u);
+        }
+        const int pos = (int)s_start[u] + (int)before + my_r[q];
         const uint8_t pix = (uint8_t)(e / d1);
         ent_pix[e0 + pos] = pix;
         ent_w[e0 + pos] = my_w[q];
@@ -429,7 +436,7 @@ int lattice_build_tiles(Lattice* L, cudaStream_t st) {
   L->bytes += (int64_t)(E_pad * (1 + 4 + 2 + 8 + 6 + 9) + sizeof(int) * (size_t)(2 * ntiles + 1));
   PL_CUDA(cudaMemsetAsync(counter, 0, 2 * sizeof(int), st));   // useg cursor, max U
   if (TE <= kFastMaxTE) {
-    const size_t smem = ((size_t)((TE + 31) / 32) * TE + 15) & ~(size_t)15;
+    const size_t smem = (size_t)TE * 4 * ((((TE + 31) / 32) + 3) / 4);
     // static (20.5 KB) + dynamic shared memory may exceed the 48 KB default: always opt in
     static PerDeviceOnce fast_attr;
     if (fast_attr.need())
