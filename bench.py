@@ -156,6 +156,33 @@ class _Pipelined:
             raise errors[0]
 
 
+def _multi_gpu_extras_isolated(rank, world):
+    """bench_extra.multi_gpu_extras in one child process per rank with its own NCCL group (next port):
+    a trap in one of the peer-memory kernels then costs the extras, not this process's JSON line."""
+    import subprocess
+    import tempfile
+    # the children rendezvous among themselves (rank 0 hosts the store), not through torchrun's agent store
+    env = {k: v for k, v in os.environ.items() if not k.startswith("TORCHELASTIC_")}
+    env["MASTER_PORT"] = str((int(os.environ.get("MASTER_PORT", "29500")) + 17) % 65000 or 29517)
+    out_path = os.path.join(tempfile.gettempdir(), f"pl_bench_extras_{env['MASTER_PORT']}.json")
+    if rank == 0 and os.path.exists(out_path):
+        os.remove(out_path)
+    try:
+        proc = subprocess.run([sys.executable, os.path.join(ROOT, "bench_extra_worker.py"), out_path], env=env,
+                              stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, timeout=600)
+        err = None if proc.returncode == 0 else (
+            f"extras worker of rank {rank} exited {proc.returncode}: " + proc.stderr.decode(errors="replace")[-600:])
+    except subprocess.TimeoutExpired:
+        err = f"extras worker of rank {rank} timed out"
+    cfgs = None
+    if rank == 0 and os.path.exists(out_path):
+        try:
+            cfgs = json.load(open(out_path))
+        except Exception as exc:
+            err = (err or "") + f" unreadable extras file: {exc!r}"
+    return cfgs, err
+
+
 def run_ours(args, rank, local_rank, world):
     import numpy as np
     import torch
@@ -366,8 +393,8 @@ def run_ours(args, rank, local_rank, world):
             if world == 1:
                 extra_cfgs = X.single_gpu_extras(pkg, dev, local_rank, flush,
                                                  with_cpu=not args.no_cpu_baseline, quick=args.quick)
-            elif hasattr(X, "multi_gpu_extras"):
-                extra_cfgs = X.multi_gpu_extras(pkg, dev, rank, local_rank, world)
+            else:
+                extra_cfgs, extra_err = _multi_gpu_extras_isolated(rank, world)
         except Exception:
             import traceback
             extra_err = traceback.format_exc()[-1500:]

@@ -331,6 +331,9 @@ def multi_gpu_extras(pkg, dev, rank, local_rank, world, steps=3, warmup=2):
                     lat.close()
 
                 ms, clocks, err = None, None, None
+                if rank == 0:
+                    import sys
+                    print(f"[bench_extra] config 4 {variant} x{world}: {mode}", file=sys.stderr, flush=True)
                 try:
                     sampler = U.ClockSampler(local_rank).start() if rank == 0 else None
                     ms = timed(step)

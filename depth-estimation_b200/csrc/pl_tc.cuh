@@ -59,7 +59,8 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return true;
     __nanosleep(256);
   }
-  printf("libpl_lattice: mbarrier wait timed out (block %d, thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
+  printf("libpl_lattice: mbarrier wait timed out (block %d of %d, thread %d of %d, barrier at shared 0x%x, parity %u)\n",
+         (int)blockIdx.x, (int)gridDim.x, (int)threadIdx.x, (int)blockDim.x, smem_u32(bar), parity);
   __trap();
   return false;
 }
