@@ -11,7 +11,7 @@ pre = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles", "r2a"
 
 
 def load(name):
-    for cand in (f"{pre}_{name}.json", os.path.join(ROOT, "profiles", f"r2h_{name}.json"), os.path.join(ROOT, "profiles", f"r2c_{name}.json"),
+    for cand in (f"{pre}_{name}.json", os.path.join(ROOT, "profiles", f"r2k_{name}.json"), os.path.join(ROOT, "profiles", f"r2h_{name}.json"),
                  os.path.join(ROOT, "profiles", f"r2a_{name}.json")):
         if os.path.exists(cand):
             return json.load(open(cand)), os.path.basename(cand)
