@@ -66,6 +66,8 @@ class ClockSampler:
     def __init__(self, gpu_index):
         self.gpu, self.thread, self.stop_flag = gpu_index, None, False
         self.sm, self.bits, self.max_mhz, self.power = [], 0, None, []
+        import threading
+        self.ready = threading.Event()     # NVML initialised, sampling has begun
 
     def _run(self):
         try:
@@ -80,6 +82,7 @@ class ClockSampler:
                     idx = self.gpu
             h = nv.nvmlDeviceGetHandleByIndex(idx)
             self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.ready.set()
             while not self.stop_flag:
                 self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
                 try:
@@ -96,11 +99,16 @@ class ClockSampler:
                 time.sleep(0.002)
         except Exception:
             pass
+        finally:
+            self.ready.set()
 
     def start(self):
+        """Returns once NVML is up and the first samples are being taken: a timed region of a few
+        milliseconds must not be over before the sampler thread has finished initialising."""
         import threading
         self.thread = threading.Thread(target=self._run, daemon=True)
         self.thread.start()
+        self.ready.wait(timeout=5.0)
         return self
 
     def stop(self):
