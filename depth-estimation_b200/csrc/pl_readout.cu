@@ -237,8 +237,10 @@ int readout_tiled(Lattice* L, const float* val, int labels, float denom, const f
                   cudaStream_t st) {
   const int d1 = L->d + 1;
   const int TE = kTile * d1;
+  // lanes per pixel: two float4 per lane where the label count allows (L = 64: 8 lanes, three shuffle
+  // rounds per reduction, the entry weights / indices amortised over 8 labels)
   int G = 1;
-  while (G < 32 && G < labels / 4) G <<= 1;
+  while (G < 32 && G < labels / 8) G <<= 1;
   // staging sized by the lattice's largest tile (at most kStageBytes): the kernel is latency bound, and
   // a 740x500 default-scale lattice needs 32 KB, not 64 -- 5 CTAs per SM instead of 3
   if (L->max_U < 0 && L->max_U_ev != nullptr) {
