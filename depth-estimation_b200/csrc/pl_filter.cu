@@ -346,6 +346,11 @@ blur_all_kernel(float* __restrict__ buf0, float* __restrict__ buf1, const int2* 
   }
 }
 
+// (Two barrier-free alternatives for these small lattices were measured and dropped, 740 x 500 x 64, M = 8 750,
+// against 27 us for this kernel: a W-channel slice of the whole lattice in ONE CTA's shared memory with
+// __syncthreads() between the passes -- 47 us, 41 us with the neighbour ids of a pass requested together --
+// and the 8-CTA cluster form over DSMEM below -- 25-39 us.  ncu puts 65 % of this kernel's stall samples in
+// grid.sync(), but a single CTA's latency chain per pass is longer still.)
 // Small lattices (a stereo frame with the module's default guide scales has M ~ 10^4
 // vertices, a few MB of values): every thread owns ITEMS (vertex, float4) items for the whole
 // blur.  Its 2(d+1) neighbour offsets are fetched once, its own value stays in registers
