@@ -394,6 +394,9 @@ class ijGuide(nn.Module):
         return _ij_grid(bs, h, w, x.device) / self.s_ij
 
 
+_PAIR_MU = {}
+
+
 def stereo_pair_depth(left, right, niters=5, gamma=.05, s=0., s_ij=.1, s_rgb=.1, window_size=9,
                       max_disp=None, criterion=None, labels=None, return_label=False):
     """Inference pipeline of the stereo notebooks with every stage on the GPU and nothing but the
@@ -415,8 +418,19 @@ def stereo_pair_depth(left, right, niters=5, gamma=.05, s=0., s_ij=.1, s_rgb=.1,
     L = int(max_disp) if max_disp is not None else w // 6
     vol = cost_volume(left, right, L, window_size, criterion if criterion is not None else AD)
     lab = None if labels is None else labels.reshape(-1).float().contiguous()
-    arange = torch.arange(L, dtype=torch.float32, device=left.device) if lab is None else lab
-    mu = charbonneir(arange[None, :], arange[:, None], gamma).contiguous()
+    if lab is None:
+        # default labels 0 .. L-1: the L x L matrix depends on (L, gamma, device) only -- a streaming caller
+        # would otherwise pay half a dozen tiny kernels per frame for it
+        key = (L, float(gamma), str(left.device))
+        mu = _PAIR_MU.get(key)
+        if mu is None:
+            arange = torch.arange(L, dtype=torch.float32, device=left.device)
+            mu = charbonneir(arange[None, :], arange[:, None], gamma).contiguous()
+            if len(_PAIR_MU) > 16:
+                _PAIR_MU.clear()
+            _PAIR_MU[key] = mu
+    else:
+        mu = charbonneir(lab[None, :], lab[:, None], gamma).contiguous()
     lat = PermutohedralLattice.from_rgb(left.permute(2, 0, 1).contiguous(), s_ij, s_rgb)
     try:
         depth, label = lat.mean_field_depth(vol.view(h * w, L), mu, niters, math.exp(s), labels=lab,

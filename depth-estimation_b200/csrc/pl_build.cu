@@ -726,11 +726,24 @@ grow_replay_kernel(const int32_t* __restrict__ vid, const uint32_t* __restrict__
     if (phase == 2) break;
     if (phase == 1) {
       const int32_t v = touch_v;
-      for (unsigned long long base = (unsigned long long)touch_after + 1; base < E; base += 8192) {
+      // 32 768 entries per trip: eight int4 loads per thread (vid is 16-byte aligned, E a multiple of 2)
+      const unsigned long long first = (unsigned long long)touch_after + 1;
+      for (unsigned long long base = first & ~3ull; base < E; base += 32768) {
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-          const unsigned long long e = base + (unsigned long long)k * 1024 + tid;
-          if (e < E && vid[e] == v) atomicMin(&touch_found, (uint32_t)e);
+          const unsigned long long e4 = base + ((unsigned long long)k * 1024 + tid) * 4;
+          if (e4 + 3 < E) {
+            const int4 x = *reinterpret_cast<const int4*>(vid + e4);
+            uint32_t hit = kQNone;
+            if (x.w == v && e4 + 3 >= first) hit = (uint32_t)(e4 + 3);
+            if (x.z == v && e4 + 2 >= first) hit = (uint32_t)(e4 + 2);
+            if (x.y == v && e4 + 1 >= first) hit = (uint32_t)(e4 + 1);
+            if (x.x == v && e4 >= first) hit = (uint32_t)e4;
+            if (hit != kQNone) atomicMin(&touch_found, hit);
+          } else {
+            for (unsigned long long e = e4 > first ? e4 : first; e < E && e < e4 + 4; e++)
+              if (vid[e] == v) atomicMin(&touch_found, (uint32_t)e);
+          }
         }
         __syncthreads();
         const uint32_t found = touch_found;
