@@ -395,6 +395,20 @@ class ijGuide(nn.Module):
 
 
 _PAIR_MU = {}
+_SIDE_STREAMS = {}
+
+
+def _side_stream(device, cur):
+    """One side stream per (device, calling stream): callers that pipeline frames over several streams keep
+    their frames independent."""
+    key = (str(device), cur.cuda_stream)
+    st = _SIDE_STREAMS.get(key)
+    if st is None:
+        if len(_SIDE_STREAMS) > 64:
+            _SIDE_STREAMS.clear()
+        st = torch.cuda.Stream(device)
+        _SIDE_STREAMS[key] = st
+    return st
 
 
 def stereo_pair_depth(left, right, niters=5, gamma=.05, s=0., s_ij=.1, s_rgb=.1, window_size=9,
@@ -416,7 +430,14 @@ def stereo_pair_depth(left, right, niters=5, gamma=.05, s=0., s_ij=.1, s_rgb=.1,
     N.require_cuda_f32(left, "left", 3)
     h, w = int(left.shape[0]), int(left.shape[1])
     L = int(max_disp) if max_disp is not None else w // 6
-    vol = cost_volume(left, right, L, window_size, criterion if criterion is not None else AD)
+    # The cost volume (all SMs, instruction bound) and the lattice build (small latency-bound kernels and one
+    # host read-back) do not depend on each other: the volume goes to a side stream and overlaps the build.
+    cur = torch.cuda.current_stream(left.device)
+    side = _side_stream(left.device, cur)
+    side.wait_stream(cur)
+    with torch.cuda.stream(side):
+        vol = cost_volume(left, right, L, window_size, criterion if criterion is not None else AD)
+    vol.record_stream(cur)
     lab = None if labels is None else labels.reshape(-1).float().contiguous()
     if lab is None:
         # default labels 0 .. L-1: the L x L matrix depends on (L, gamma, device) only -- a streaming caller
@@ -432,6 +453,7 @@ def stereo_pair_depth(left, right, niters=5, gamma=.05, s=0., s_ij=.1, s_rgb=.1,
     else:
         mu = charbonneir(lab[None, :], lab[:, None], gamma).contiguous()
     lat = PermutohedralLattice.from_rgb(left.permute(2, 0, 1).contiguous(), s_ij, s_rgb)
+    cur.wait_stream(side)
     try:
         depth, label = lat.mean_field_depth(vol.view(h * w, L), mu, niters, math.exp(s), labels=lab,
                                             want_label=return_label)
