@@ -85,6 +85,7 @@ static void lattice_release(Lattice* L, cudaStream_t st) {
   dev_free(L->rec_splat, st);
   dev_free(L->val[0], st);
   dev_free(L->val[1], st);
+  dev_free(L->flow, st);
   if (L->max_U_ev != nullptr) cudaEventDestroy(L->max_U_ev);
   delete L;
 }
@@ -484,7 +485,10 @@ static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT
     // One kernel per iteration (pl_fused_tc.cu on the tensor cores, pl_fused.cu on the CUDA
     // cores): P lives in work_dev and is updated in place (a tile reads its own rows of
     // P_prev into registers before it writes them).
-    PL_TRY(pl::lattice_workspace(Lt, L, st));
+    // small lattices: the blur has no grid barrier and cannot zero its own input, so three value
+    // buffers rotate (result / zeroed next target / free) instead of two
+    const bool rotate = pl::lattice_blur_is_flow(Lt, L);
+    PL_TRY(pl::lattice_workspace(Lt, L, st, rotate));
     float* mu_canon = nullptr;
     if (use_tc) {
       PL_TRY(pl::dev_alloc((void**)&mu_canon, pl::mf_tc_mu_bytes(L), st));
@@ -492,12 +496,11 @@ static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT
     }
     const size_t row = sizeof(float) * (size_t)L;
     float* res = nullptr;           // buffer holding the blurred lattice of the previous iteration
+    float* target = Lt->val[0];     // the splat target: zeroed here (first iteration) or by the previous blur
+    float* other = Lt->val[1];      // where the blur may write
     PL_CUDA(cudaMemsetAsync(Lt->val[1] + (size_t)Lt->M * L, 0, row, st));
     PL_CUDA(cudaMemsetAsync(Lt->val[0], 0, row * (size_t)(Lt->M + 1), st));
     for (int it = 0; it < niters; it++) {
-      // the splat target: zeroed above (first iteration) or by the previous blur
-      float* target = (res == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
-      float* other = (target == Lt->val[0]) ? Lt->val[1] : Lt->val[0];
       if (use_ws) {
         PL_TRY(pl::mf_ws_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev, mu_canon,
                                    scale, L, st));
@@ -508,7 +511,21 @@ static int meanfield_impl(pl_lattice* lat, const float* e0_dev, const float* muT
         PL_TRY(pl::mf_fused_iteration(Lt, it == 0, res, target, e0_dev, work_dev, work_dev,
                                       muT_dev, scale, L, st));
       }
-      PL_TRY(pl::lattice_blur(Lt, target, other, L, st, &res, it + 1 < niters));
+      // the iteration kernel is done with `res`: it is the buffer nothing touches during the blur
+      float* spare = rotate ? (res != nullptr ? res : Lt->val[2]) : nullptr;
+      float* zeroed = nullptr;
+      float* out = nullptr;
+      PL_TRY(pl::lattice_blur(Lt, target, other, L, st, &out, it + 1 < niters, spare, &zeroed));
+      if (zeroed != nullptr) {       // rotation: result in `other`, next target = the zeroed spare
+        float* input = target;
+        target = zeroed;
+        other = input;
+      } else if (out == target) {    // in place: `other` was zeroed (or this was the last iteration)
+        float* t = target;
+        target = other;
+        other = t;
+      }                              // else: result in `other`, `target` was zeroed again
+      res = out;
     }
     pl::dev_free(mu_canon, st);
     // E = E0 + (slice - P) of the last iteration (crf_module.py:101,103)

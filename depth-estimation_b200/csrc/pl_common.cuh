@@ -112,9 +112,16 @@ struct Lattice {
   int mean_U = 0;              // mean distinct-vertex count per tile (same read-back)
   int* h_max_U = nullptr;
   cudaEvent_t max_U_ev = nullptr;
-  // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats
-  float* val[2] = {nullptr, nullptr};
+  // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats, and a third one for the
+  // mean-field loop's buffer rotation on small lattices (lattice_workspace(..., third = true))
+  float* val[3] = {nullptr, nullptr, nullptr};
   int64_t ws_floats = 0;     // floats per buffer
+  // scratch of the barrier-free small-lattice blur (pl_filter.cu blur_flow_kernel): two sets of d
+  // pass buffers of M x flow_C floats; set `flow_set` is all-sentinel and is the one the next call uses
+  float* flow = nullptr;
+  int64_t flow_floats = 0;   // floats per pass buffer
+  int flow_set = 0;
+  int64_t flow_dirty[2] = {0, 0};   // floats from the start of each pass buffer of a set that may not be sentinel
   int64_t bytes = 0;         // persistent device bytes
 };
 
@@ -147,9 +154,13 @@ int slice_tiled(Lattice* L, const float* val, int Cc, float denom, float* dst, i
 int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, int64_t dst_stride,
                   int C, const float* sub, int64_t sub_stride, const float* add, int64_t add_stride,
                   uint32_t flags, cudaStream_t st);
-int lattice_workspace(Lattice* L, int Cc, cudaStream_t st);
+int lattice_workspace(Lattice* L, int Cc, cudaStream_t st, bool third = false);
+bool lattice_blur_is_flow(const Lattice* L, int Cc);
+// `zero_other`: leave a zeroed buffer behind for the next splat -- the one of cur / nxt that does not
+// hold the result, unless `zeroed` is given and comes back non-null: then it names the buffer that was
+// zeroed instead (`spare`, a third buffer of the same shape that nothing reads while the blur runs).
 int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out,
-                 bool zero_other = false);
+                 bool zero_other = false, float* spare = nullptr, float** zeroed = nullptr);
 // fused mean-field iteration (pl_fused.cu)
 bool mf_fused_supported(const Lattice* L, int labels);
 int mf_fused_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,

@@ -414,6 +414,118 @@ blur_reg_kernel(float* __restrict__ buf0, float* __restrict__ buf1, const int2* 
   }
 }
 
+// (Also measured and dropped on these lattices: TWO axes per pass -- three grid barriers instead of six,
+// 8 gathers per item and pass instead of 2 x 2, bit-identical -- 34.4 us against 26.5: a pass is not only
+// the barrier, the uncached gathers of rows other SMs have just written cost as much again, and they
+// scale with the gather count.)
+// The same lattices WITHOUT any barrier between the passes (26.5 -> 14 us at M = 8 750 x 64 channels).
+// Every pass writes its own scratch buffer (pass j -> flow[j], the last one -> the result buffer), all
+// pre-filled with a sentinel bit pattern no arithmetic result can have: 0xFFFFFFFF, a NaN payload the
+// FMA unit never produces (a NaN result is always 0x7FFFFFFF).  A thread of pass j + 1 re-reads its two
+// neighbour values from flow[j] until none of the four components is the sentinel.  Each 32-bit component
+// is written exactly once per call, so a non-sentinel component is final and the four need no joint
+// atomicity; nothing is ordered against anything else, so there is no counter and no flag.  Per pass the
+// chain is a store becoming visible plus the neighbour's load round trip, instead of fence + atomic
+// arrival + flag poll + load.  (The fence behind the store is not needed for correctness; it makes the
+// store visible sooner: 16.3 -> 14 us.  Backing off between polls costs 4 us.)
+// The sentinel state is restored by the NEXT call: the scratch has two sets, a call uses set s and
+// refills set 1 - s with fire-and-forget stores.  The launch is cooperative only for its co-residency
+// guarantee: every producer must be running.  Row M (absent neighbour) is never read, the id is tested
+// instead.  `buf0` is only read and cannot be zeroed here -- another thread may still be reading it in
+// pass 0 when this one is done -- so the next splat target is a THIRD buffer, `zero_buf`, that nothing
+// else touches while this kernel runs (the mean-field loop rotates three value buffers), or the caller
+// clears buf0 behind the kernel.
+// Same fp32 operations in the same order as blur_reg_kernel: bit-identical results
+// (tests/test_blur_forms_gpu.py).  A poll that never succeeds traps after ~2 s.
+constexpr uint32_t kFlowSentinel = 0xFFFFFFFFu;
+__device__ __forceinline__ float4 ld_relaxed_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_f4(float* p, const float4& v) {
+  asm volatile("st.relaxed.gpu.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ bool flow_ready(const float4& v) {
+  return __float_as_uint(v.x) != kFlowSentinel && __float_as_uint(v.y) != kFlowSentinel &&
+         __float_as_uint(v.z) != kFlowSentinel && __float_as_uint(v.w) != kFlowSentinel;
+}
+__global__ void __launch_bounds__(kBlurRegThreads, 2)
+blur_flow_kernel(const float* __restrict__ buf0, float* __restrict__ result, float* __restrict__ flow_use,
+                 float* __restrict__ flow_refill, size_t flow_stride, float* __restrict__ zero_buf,
+                 const int2* __restrict__ nbr, uint32_t M, int Cc) {
+  constexpr int D1 = 6;
+  const uint32_t V = (uint32_t)(Cc / 4);
+  const uint32_t total = M * V;
+  const uint32_t t = (uint32_t)blockIdx.x * kBlurRegThreads + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t v = t / V;
+  const uint32_t c = (t - v * V) * 4;
+  const uint32_t off = v * (uint32_t)Cc + c;
+  int2 own[D1];
+#pragma unroll
+  for (int j = 0; j < D1; j++) own[j] = nbr[(size_t)j * M + v];
+  float4 val = __ldcg(reinterpret_cast<const float4*>(buf0 + off));
+  {
+    const float sf = __uint_as_float(kFlowSentinel);
+    const float4 s4 = make_float4(sf, sf, sf, sf);
+#pragma unroll
+    for (int j = 0; j < D1 - 1; j++) *reinterpret_cast<float4*>(flow_refill + j * flow_stride + off) = s4;
+    if (zero_buf != nullptr) *reinterpret_cast<float4*>(zero_buf + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < D1; j++) {
+    const uint32_t ia = (uint32_t)own[j].x, ib = (uint32_t)own[j].y;
+    float4 a = zero, b = zero;
+    if (j == 0) {   // the input is complete before the launch
+      if (ia < M) a = __ldcg(reinterpret_cast<const float4*>(buf0 + ia * (uint32_t)Cc + c));
+      if (ib < M) b = __ldcg(reinterpret_cast<const float4*>(buf0 + ib * (uint32_t)Cc + c));
+    } else {
+      const float* in = flow_use + (size_t)(j - 1) * flow_stride;
+      const float* pa = in + ia * (uint32_t)Cc + c;
+      const float* pb = in + ib * (uint32_t)Cc + c;
+      bool ra = ia >= M, rb = ib >= M;
+      uint32_t spins = 0;
+      while (!(ra && rb)) {
+        float4 ta = zero, tb = zero;
+        if (!ra) ta = ld_relaxed_f4(pa);
+        if (!rb) tb = ld_relaxed_f4(pb);
+        if (!ra && flow_ready(ta)) {
+          a = ta;
+          ra = true;
+        }
+        if (!rb && flow_ready(tb)) {
+          b = tb;
+          rb = true;
+        }
+        if (++spins > (1u << 22)) {
+          printf("libpl_lattice: blur_flow_kernel: pass %d never saw its neighbours (block %d, thread %d)\n", j,
+                 (int)blockIdx.x, (int)threadIdx.x);
+          __trap();
+        }
+      }
+    }
+    float4 r;
+    r.x = __fmaf_rn(0.5f, b.x, __fmaf_rn(0.5f, a.x, val.x));
+    r.y = __fmaf_rn(0.5f, b.y, __fmaf_rn(0.5f, a.y, val.y));
+    r.z = __fmaf_rn(0.5f, b.z, __fmaf_rn(0.5f, a.z, val.z));
+    r.w = __fmaf_rn(0.5f, b.w, __fmaf_rn(0.5f, a.w, val.w));
+    val = r;
+    if (j < D1 - 1) {
+      st_relaxed_f4(flow_use + (size_t)j * flow_stride + off, r);
+      __threadfence();
+    } else {
+      *reinterpret_cast<float4*>(result + off) = r;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // blur inside thread-block clusters, no grid-wide barrier.
 //
@@ -579,24 +691,39 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
 }  // namespace
 
 // Grow-only ping-pong value buffers of (M+1) x Cc floats.
-int lattice_workspace(Lattice* L, int Cc, cudaStream_t st) {
+int lattice_workspace(Lattice* L, int Cc, cudaStream_t st, bool third) {
   const int64_t need = (L->M + 1) * (int64_t)Cc;
-  if (L->ws_floats >= need) return PL_OK;
-  for (int k = 0; k < 2; k++) {
-    if (L->val[k]) dev_free(L->val[k], st);
-    L->val[k] = nullptr;
+  if (L->ws_floats < need) {
+    for (int k = 0; k < 3; k++) {
+      if (L->val[k]) dev_free(L->val[k], st);
+      L->val[k] = nullptr;
+    }
+    L->ws_floats = 0;
+    PL_TRY(dev_alloc((void**)&L->val[0], sizeof(float) * (size_t)need, st));
+    PL_TRY(dev_alloc((void**)&L->val[1], sizeof(float) * (size_t)need, st));
+    L->ws_floats = need;
   }
-  L->ws_floats = 0;
-  PL_TRY(dev_alloc((void**)&L->val[0], sizeof(float) * (size_t)need, st));
-  PL_TRY(dev_alloc((void**)&L->val[1], sizeof(float) * (size_t)need, st));
-  L->ws_floats = need;
+  if (third && L->val[2] == nullptr)
+    PL_TRY(dev_alloc((void**)&L->val[2], sizeof(float) * (size_t)L->ws_floats, st));
   return PL_OK;
+}
+
+// whether lattice_blur takes the barrier-free form for this shape (the mean-field loop then rotates
+// three value buffers so that the next splat target is zeroed inside the blur kernel).
+// PL_BLUR_FORM=reg (read per call: tests/test_blur_forms_gpu.py flips it) keeps the grid-barrier forms.
+bool lattice_blur_is_flow(const Lattice* L, int Cc) {
+  const uint64_t vtx_items = (uint64_t)L->M * (uint64_t)(Cc / 4);
+  const char* form = getenv("PL_BLUR_FORM");
+  if (form != nullptr && form[0] == 'r') return false;
+  return L->d == 5 && Cc % 4 == 0 && L->M > 0 && (uint64_t)(L->M + 1) * Cc < 0x7fffffffull &&
+         vtx_items <= (uint64_t)PL_SM_COUNT * 2 * kBlurRegThreads;
 }
 
 // d+1 Jacobi passes starting from `cur` (scratch `nxt`); *out = buffer holding the result.
 // Both buffers must have a zero row M.  Cc % 4 == 0.
 int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, float** out,
-                 bool zero_other) {
+                 bool zero_other, float* spare, float** zeroed) {
+  if (zeroed != nullptr) *zeroed = nullptr;
   const int D1 = L->d + 1;
   const int64_t M = L->M;
   const uint64_t vtx_items = (uint64_t)M * (uint64_t)(Cc / 4);
@@ -634,6 +761,65 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
               (uint32_t)M, Cc, D1, per, zero_other ? 1 : 0);
     *out = cur;
     return PL_OK;
+  }
+  // barrier-free form: at most one item per thread on 2 x 148 co-resident CTAs
+  if (coop_ctas_per_sm > 0 && lattice_blur_is_flow(L, Cc)) {
+    static int flow_occ[64];
+    static PerDeviceOnce flow_once;
+    if (flow_once.need()) {
+      int o = 0;
+      flow_occ[devi] = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, blur_flow_kernel, kBlurRegThreads, 0) ==
+                               cudaSuccess ? o : 0;
+    }
+    if (flow_occ[devi] >= 2) {
+      const int64_t per = M * (int64_t)Cc;
+      if (L->flow_floats < per) {
+        dev_free(L->flow, st);
+        L->flow = nullptr;
+        L->flow_floats = 0;
+        PL_TRY(dev_alloc((void**)&L->flow, sizeof(float) * (size_t)per * 10, st));
+        L->flow_floats = per;
+        L->flow_set = 0;
+        L->flow_dirty[0] = 0;
+        L->flow_dirty[1] = per;     // uninitialised memory: to be refilled in full
+        PL_CUDA(cudaMemsetAsync(L->flow, 0xFF, sizeof(float) * (size_t)per * 5, st));
+      }
+      const int s_use = L->flow_set, s_fill = 1 - s_use;
+      const size_t stride = (size_t)L->flow_floats;
+      float* use = L->flow + (size_t)s_use * 5 * stride;
+      float* refill = L->flow + (size_t)s_fill * 5 * stride;
+      // the kernel refills [0, per) of every pass buffer of the other set; a wider stretch left by a
+      // call with more channels is refilled here
+      if (L->flow_dirty[s_fill] > per) {
+        for (int j = 0; j < 5; j++)
+          PL_CUDA(cudaMemsetAsync(refill + j * stride + per, 0xFF,
+                                  sizeof(float) * (size_t)(L->flow_dirty[s_fill] - per), st));
+      }
+      L->flow_dirty[s_fill] = 0;
+      L->flow_dirty[s_use] = per;
+      L->flow_set = s_fill;
+      unsigned grid = ceil_div_u(vtx_items, (uint64_t)kBlurRegThreads);
+      uint32_t M32 = (uint32_t)M;
+      const int2* nbr = L->nbr;
+      const float* in0 = cur;
+      // the next splat target: `spare` zeroed inside the kernel, else `cur` by a memset behind it
+      float* zb = (zero_other && zeroed != nullptr && spare != nullptr && spare != cur && spare != nxt) ? spare
+                                                                                                       : nullptr;
+      size_t stride_arg = stride;
+      void* args[] = {&in0, &nxt, &use, &refill, &stride_arg, &zb, &nbr, &M32, &Cc};
+      if (g_prof_on) prof_begin("blur_flow_kernel", st);
+      cudaError_t e = cudaLaunchCooperativeKernel((const void*)blur_flow_kernel, dim3(grid), dim3(kBlurRegThreads),
+                                                  args, 0, st);
+      if (g_prof_on) prof_end(st);
+      g_launches++;
+      PL_CUDA(e);
+      if (zb != nullptr)
+        *zeroed = zb;
+      else if (zero_other)
+        PL_CUDA(cudaMemsetAsync(cur, 0, sizeof(float) * (size_t)M * Cc, st));
+      *out = nxt;
+      return PL_OK;
+    }
   }
   // register-resident variant: d = 5 and at most 2 items per thread on 2 x 148 CTAs
   if (coop_ctas_per_sm > 0 && D1 == 6 && (uint64_t)(M + 1) * Cc < 0x7fffffffull &&
