@@ -47,6 +47,69 @@ extern bool g_prof_on;
     PL_CUDA(cudaGetLastError());                                   \
   } while (0)
 
+// Programmatic dependent launch: a kernel launched with `pdl` may start while the kernel in front of
+// it in the stream is still running; it must not read anything that kernel writes (nor write what it
+// reads) before pdl_wait(), which returns once that kernel has completed and its writes are visible.
+// pdl_launch_dependents() (after pdl_wait(), so completion stays transitive along the stream) lets
+// the NEXT kernel begin its own prologue.  Both are no-ops in a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// PL_NO_PDL (environment, read once) launches everything the ordinary way: A/B timing knob.
+inline bool pdl_enabled() {
+  static const bool on = getenv("PL_NO_PDL") == nullptr;
+  return on;
+}
+
+inline cudaError_t launch_ex(const void* fn, dim3 grid, dim3 block, size_t smem, cudaStream_t st, void** args,
+                             bool cooperative, bool pdl) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  unsigned na = 0;
+  if (cooperative) {
+    at[na].id = cudaLaunchAttributeCooperative;
+    at[na].val.cooperative = 1;
+    na++;
+  }
+  if (pdl && pdl_enabled()) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    na++;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelExC(&cfg, fn, args);
+}
+
+// PL_LAUNCH for a kernel that calls pdl_wait(): launched so that it may start under the tail of the
+// kernel in front of it.  Only where that kernel is one of ours (not a memset or a copy).
+inline cudaLaunchConfig_t pdl_config(dim3 grid, dim3 block, size_t smem, cudaStream_t st, cudaLaunchAttribute* at) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cfg;
+}
+#define PL_LAUNCH_PDL(kernel, grid, block, smem, stream, ...)                                       \
+  do {                                                                                              \
+    if (pl::g_prof_on) pl::prof_begin(#kernel, (stream));                                           \
+    cudaLaunchAttribute at_[1];                                                                     \
+    cudaLaunchConfig_t cfg_ = pl::pdl_config(dim3(grid), dim3(block), (smem), (stream), at_);       \
+    cudaError_t e_ = cudaLaunchKernelEx(&cfg_, kernel, __VA_ARGS__);                                \
+    if (pl::g_prof_on) pl::prof_end((stream));                                                      \
+    pl::g_launches++;                                                                               \
+    PL_CUDA(e_);                                                                                    \
+  } while (0)
+
 // Opt-in attributes (cudaFuncSetAttribute) are per DEVICE: a process that drives several GPUs has
 // to set them once on each.  `static PerDeviceOnce once; if (once.need()) { ... }`
 struct PerDeviceOnce {

@@ -455,37 +455,56 @@ __device__ __forceinline__ bool flow_ready(const float4& v) {
   return __float_as_uint(v.x) != kFlowSentinel && __float_as_uint(v.y) != kFlowSentinel &&
          __float_as_uint(v.z) != kFlowSentinel && __float_as_uint(v.w) != kFlowSentinel;
 }
+// ITEMS: adjacent float4 channel groups of ONE vertex per thread (they share the neighbour ids).
+template <int ITEMS>
 __global__ void __launch_bounds__(kBlurRegThreads, 2)
 blur_flow_kernel(const float* __restrict__ buf0, float* __restrict__ result, float* __restrict__ flow_use,
                  float* __restrict__ flow_refill, size_t flow_stride, float* __restrict__ zero_buf,
                  const int2* __restrict__ nbr, uint32_t M, int Cc) {
   constexpr int D1 = 6;
-  const uint32_t V = (uint32_t)(Cc / 4);
-  const uint32_t total = M * V;
+  const uint32_t VT = (uint32_t)(Cc / (4 * ITEMS));     // threads per vertex
+  const uint32_t total = M * VT;
   const uint32_t t = (uint32_t)blockIdx.x * kBlurRegThreads + threadIdx.x;
   if (t >= total) return;
-  const uint32_t v = t / V;
-  const uint32_t c = (t - v * V) * 4;
+  const uint32_t v = t / VT;
+  const uint32_t c = (t - v * VT) * (4 * ITEMS);
   const uint32_t off = v * (uint32_t)Cc + c;
   int2 own[D1];
 #pragma unroll
   for (int j = 0; j < D1; j++) own[j] = nbr[(size_t)j * M + v];
-  float4 val = __ldcg(reinterpret_cast<const float4*>(buf0 + off));
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
   {
     const float sf = __uint_as_float(kFlowSentinel);
     const float4 s4 = make_float4(sf, sf, sf, sf);
 #pragma unroll
-    for (int j = 0; j < D1 - 1; j++) *reinterpret_cast<float4*>(flow_refill + j * flow_stride + off) = s4;
-    if (zero_buf != nullptr) *reinterpret_cast<float4*>(zero_buf + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j = 0; j < D1 - 1; j++)
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++)
+        *reinterpret_cast<float4*>(flow_refill + j * flow_stride + off + 4 * i) = s4;
   }
-  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  // the neighbour table and the other scratch set are nobody else's business; the input and the spare
+  // buffer belong to the kernel in front until it has completed (programmatic dependent launch)
+  pdl_wait();
+  pdl_launch_dependents();
+  float4 val[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; i++) val[i] = __ldcg(reinterpret_cast<const float4*>(buf0 + off + 4 * i));
+  if (zero_buf != nullptr) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) *reinterpret_cast<float4*>(zero_buf + off + 4 * i) = zero;
+  }
 #pragma unroll
   for (int j = 0; j < D1; j++) {
     const uint32_t ia = (uint32_t)own[j].x, ib = (uint32_t)own[j].y;
-    float4 a = zero, b = zero;
+    float4 a[ITEMS], b[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) a[i] = b[i] = zero;
     if (j == 0) {   // the input is complete before the launch
-      if (ia < M) a = __ldcg(reinterpret_cast<const float4*>(buf0 + ia * (uint32_t)Cc + c));
-      if (ib < M) b = __ldcg(reinterpret_cast<const float4*>(buf0 + ib * (uint32_t)Cc + c));
+#pragma unroll
+      for (int i = 0; i < ITEMS; i++) {
+        if (ia < M) a[i] = __ldcg(reinterpret_cast<const float4*>(buf0 + ia * (uint32_t)Cc + c + 4 * i));
+        if (ib < M) b[i] = __ldcg(reinterpret_cast<const float4*>(buf0 + ib * (uint32_t)Cc + c + 4 * i));
+      }
     } else {
       const float* in = flow_use + (size_t)(j - 1) * flow_stride;
       const float* pa = in + ia * (uint32_t)Cc + c;
@@ -493,16 +512,23 @@ blur_flow_kernel(const float* __restrict__ buf0, float* __restrict__ result, flo
       bool ra = ia >= M, rb = ib >= M;
       uint32_t spins = 0;
       while (!(ra && rb)) {
-        float4 ta = zero, tb = zero;
-        if (!ra) ta = ld_relaxed_f4(pa);
-        if (!rb) tb = ld_relaxed_f4(pb);
-        if (!ra && flow_ready(ta)) {
-          a = ta;
-          ra = true;
+        if (!ra) {
+          bool ok = true;
+#pragma unroll
+          for (int i = 0; i < ITEMS; i++) {
+            a[i] = ld_relaxed_f4(pa + 4 * i);
+            ok = ok && flow_ready(a[i]);
+          }
+          ra = ok;
         }
-        if (!rb && flow_ready(tb)) {
-          b = tb;
-          rb = true;
+        if (!rb) {
+          bool ok = true;
+#pragma unroll
+          for (int i = 0; i < ITEMS; i++) {
+            b[i] = ld_relaxed_f4(pb + 4 * i);
+            ok = ok && flow_ready(b[i]);
+          }
+          rb = ok;
         }
         if (++spins > (1u << 22)) {
           printf("libpl_lattice: blur_flow_kernel: pass %d never saw its neighbours (block %d, thread %d)\n", j,
@@ -511,18 +537,20 @@ blur_flow_kernel(const float* __restrict__ buf0, float* __restrict__ result, flo
         }
       }
     }
-    float4 r;
-    r.x = __fmaf_rn(0.5f, b.x, __fmaf_rn(0.5f, a.x, val.x));
-    r.y = __fmaf_rn(0.5f, b.y, __fmaf_rn(0.5f, a.y, val.y));
-    r.z = __fmaf_rn(0.5f, b.z, __fmaf_rn(0.5f, a.z, val.z));
-    r.w = __fmaf_rn(0.5f, b.w, __fmaf_rn(0.5f, a.w, val.w));
-    val = r;
-    if (j < D1 - 1) {
-      st_relaxed_f4(flow_use + (size_t)j * flow_stride + off, r);
-      __threadfence();
-    } else {
-      *reinterpret_cast<float4*>(result + off) = r;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      float4 r;
+      r.x = __fmaf_rn(0.5f, b[i].x, __fmaf_rn(0.5f, a[i].x, val[i].x));
+      r.y = __fmaf_rn(0.5f, b[i].y, __fmaf_rn(0.5f, a[i].y, val[i].y));
+      r.z = __fmaf_rn(0.5f, b[i].z, __fmaf_rn(0.5f, a[i].z, val[i].z));
+      r.w = __fmaf_rn(0.5f, b[i].w, __fmaf_rn(0.5f, a[i].w, val[i].w));
+      val[i] = r;
+      if (j < D1 - 1)
+        st_relaxed_f4(flow_use + (size_t)j * flow_stride + off + 4 * i, r);
+      else
+        *reinterpret_cast<float4*>(result + off + 4 * i) = r;
     }
+    if (j < D1 - 1) __threadfence();
   }
 }
 
@@ -711,13 +739,18 @@ int lattice_workspace(Lattice* L, int Cc, cudaStream_t st, bool third) {
 // whether lattice_blur takes the barrier-free form for this shape (the mean-field loop then rotates
 // three value buffers so that the next splat target is zeroed inside the blur kernel).
 // PL_BLUR_FORM=reg (read per call: tests/test_blur_forms_gpu.py flips it) keeps the grid-barrier forms.
-bool lattice_blur_is_flow(const Lattice* L, int Cc) {
-  const uint64_t vtx_items = (uint64_t)L->M * (uint64_t)(Cc / 4);
+// items per thread of the barrier-free form for this shape; 0: not applicable
+static int blur_flow_items(const Lattice* L, int Cc) {
   const char* form = getenv("PL_BLUR_FORM");
-  if (form != nullptr && form[0] == 'r') return false;
-  return L->d == 5 && Cc % 4 == 0 && L->M > 0 && (uint64_t)(L->M + 1) * Cc < 0x7fffffffull &&
-         vtx_items <= (uint64_t)PL_SM_COUNT * 2 * kBlurRegThreads;
+  if (form != nullptr && form[0] == 'r') return 0;
+  if (L->d != 5 || Cc % 4 != 0 || L->M <= 0 || (uint64_t)(L->M + 1) * Cc >= 0x7fffffffull) return 0;
+  const uint64_t vtx_items = (uint64_t)L->M * (uint64_t)(Cc / 4);
+  const uint64_t threads = (uint64_t)PL_SM_COUNT * 2 * kBlurRegThreads;
+  if (vtx_items <= threads) return 1;
+  if (Cc % 8 == 0 && vtx_items <= 2 * threads) return 2;
+  return 0;
 }
+bool lattice_blur_is_flow(const Lattice* L, int Cc) { return blur_flow_items(L, Cc) > 0; }
 
 // d+1 Jacobi passes starting from `cur` (scratch `nxt`); *out = buffer holding the result.
 // Both buffers must have a zero row M.  Cc % 4 == 0.
@@ -762,18 +795,23 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
     *out = cur;
     return PL_OK;
   }
-  // barrier-free form: at most one item per thread on 2 x 148 co-resident CTAs
-  if (coop_ctas_per_sm > 0 && lattice_blur_is_flow(L, Cc)) {
+  // barrier-free form: one or two items per thread on 2 x 148 co-resident CTAs
+  const int flow_items = coop_ctas_per_sm > 0 ? blur_flow_items(L, Cc) : 0;
+  if (flow_items > 0) {
     static int flow_occ[64];
     static PerDeviceOnce flow_once;
     if (flow_once.need()) {
-      int o = 0;
-      flow_occ[devi] = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, blur_flow_kernel, kBlurRegThreads, 0) ==
-                               cudaSuccess ? o : 0;
+      int o1 = 0, o2 = 0;
+      const bool ok = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, blur_flow_kernel<1>, kBlurRegThreads, 0) ==
+                          cudaSuccess &&
+                      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, blur_flow_kernel<2>, kBlurRegThreads, 0) ==
+                          cudaSuccess;
+      flow_occ[devi] = ok ? (o1 < o2 ? o1 : o2) : 0;
     }
     if (flow_occ[devi] >= 2) {
       const int64_t per = M * (int64_t)Cc;
-      if (L->flow_floats < per) {
+      const bool fresh = L->flow_floats < per;   // a memset sits in front of this launch
+      if (fresh) {
         dev_free(L->flow, st);
         L->flow = nullptr;
         L->flow_floats = 0;
@@ -798,7 +836,7 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
       L->flow_dirty[s_fill] = 0;
       L->flow_dirty[s_use] = per;
       L->flow_set = s_fill;
-      unsigned grid = ceil_div_u(vtx_items, (uint64_t)kBlurRegThreads);
+      unsigned grid = ceil_div_u(vtx_items / flow_items, (uint64_t)kBlurRegThreads);
       uint32_t M32 = (uint32_t)M;
       const int2* nbr = L->nbr;
       const float* in0 = cur;
@@ -808,8 +846,9 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
       size_t stride_arg = stride;
       void* args[] = {&in0, &nxt, &use, &refill, &stride_arg, &zb, &nbr, &M32, &Cc};
       if (g_prof_on) prof_begin("blur_flow_kernel", st);
-      cudaError_t e = cudaLaunchCooperativeKernel((const void*)blur_flow_kernel, dim3(grid), dim3(kBlurRegThreads),
-                                                  args, 0, st);
+      const void* fn = flow_items == 1 ? (const void*)blur_flow_kernel<1> : (const void*)blur_flow_kernel<2>;
+      // programmatic dependent launch unless a memset sits in front (the scratch was just allocated)
+      cudaError_t e = launch_ex(fn, dim3(grid), dim3(kBlurRegThreads), 0, st, args, true, !fresh);
       if (g_prof_on) prof_end(st);
       g_launches++;
       PL_CUDA(e);

@@ -134,6 +134,16 @@ __global__ void __launch_bounds__(kThreads, 1) mf_ws_kernel(const WsArgs a) {
       for (int b = 5; b < 7; b++) tc::mbar_init(&bars[b], kMain);
       for (int b = 7; b < 9; b++) tc::mbar_init(&bars[b], kSplat);
       tc::fence_mbar_init();
+    }
+    __syncwarp();
+    tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tc::tcgen05_fence_before();
+  }
+  // up to here nothing of the previous kernel's output has been touched (programmatic dependent launch)
+  pdl_wait();
+  pdl_launch_dependents();
+  if (warp == 0) {
+    if (lane == 0) {
       tc::mbar_arrive_expect_tx(&bars[0], 2 * C::B_BYTES);
       tc::tma_load_1d(s_mu, a.mu_canon, 2 * C::B_BYTES, &bars[0]);
       for (uint32_t k = 0; k < 2 && k < my_tiles; k++) {   // splat records of the first two tiles
@@ -142,9 +152,6 @@ __global__ void __launch_bounds__(kThreads, 1) mf_ws_kernel(const WsArgs a) {
                         9 * kTE, &bars[3 + k]);
       }
     }
-    __syncwarp();
-    tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
-    tc::tcgen05_fence_before();
   }
   __syncthreads();
   tc::tcgen05_fence_after();
@@ -450,6 +457,10 @@ int launch_ws(const WsArgs& a, cudaStream_t st) {
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
   }
   const unsigned grid = (unsigned)(a.ntiles < PL_SM_COUNT ? a.ntiles : PL_SM_COUNT);
+  if (!FIRST) {   // behind a blur kernel of ours; the first iteration follows memsets
+    PL_LAUNCH_PDL((mf_ws_kernel<L, FIRST>), grid, kThreads, C::SMEM, st, a);
+    return PL_OK;
+  }
   PL_LAUNCH((mf_ws_kernel<L, FIRST>), grid, kThreads, C::SMEM, st, a);
   return PL_OK;
 }

@@ -68,7 +68,7 @@ __device__ __forceinline__ void red_group(Red& r, int G) {
 
 // One CTA per tile of 128 pixels; G lanes per pixel (power of two, <= 32), each lane owns the
 // float4 columns lane, lane + G, ... of the pixel's L labels.
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 3)     // 80 registers: 3 CTAs per SM beat 4 with spills and 2 with 123
 readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
                      const uint16_t* __restrict__ loc, const float* __restrict__ bary,
                      const int32_t* __restrict__ vid, const int2* __restrict__ useg,
@@ -91,6 +91,14 @@ readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
   const int V = L >> 2;
   const bool staged = (size_t)U * L * 4 <= (size_t)stage_bytes;
 
+  // the tile's records first: they belong to the lattice, not to the kernel in front of this one
+  const int valid = rows * d1;
+  for (int i = tid; i < valid; i += kThreads) {
+    s_w[i] = bary[tile * TE + i] * inv_denom;
+    s_idx[i] = staged ? (int)loc[tile * TE + i] : vid[tile * TE + i];
+  }
+  for (int i = tid; i < L; i += kThreads) s_lab[i] = labels ? labels[i] : (float)i;
+  pdl_wait();      // the blurred lattice, P and E0 from here on (programmatic dependent launch)
   if (staged) {
     const int2* seg = useg + tile_off[tile];
     for (int i = tid; i < U * V; i += kThreads) {
@@ -99,12 +107,6 @@ readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
           *reinterpret_cast<const float4*>(val + (int64_t)seg[u].x * L + 4 * v);
     }
   }
-  const int valid = rows * d1;
-  for (int i = tid; i < valid; i += kThreads) {
-    s_w[i] = bary[tile * TE + i] * inv_denom;
-    s_idx[i] = staged ? (int)loc[tile * TE + i] : vid[tile * TE + i];
-  }
-  for (int i = tid; i < L; i += kThreads) s_lab[i] = labels ? labels[i] : (float)i;
   __syncthreads();
 
   const int g = tid / G, l = tid % G, groups = kThreads / G;
@@ -114,6 +116,36 @@ readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
     // an exp and a branch per element plus five shuffles and two exps per merge step.
     for (int r = g; r < rows; r += groups) {
       const int64_t px = p0 + r;
+      // P and E0 of this lane's columns first: their HBM latency runs under the gathers below
+      float4 pp[4], ee[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int v = l + k * G;
+        if (v < V) {
+          pp[k] = *reinterpret_cast<const float4*>(p + px * L + 4 * v);
+          ee[k] = *reinterpret_cast<const float4*>(e0 + px * L + 4 * v);
+        }
+      }
+      // vertex-major: weight and row index of a vertex are read once for the lane's (up to) four columns;
+      // per (pixel, label) the sum still runs over the d+1 vertices in entry order
+      float4 acc[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < d1; j++) {
+        const float w = s_w[r * d1 + j];
+        const int ix = s_idx[r * d1 + j];
+        const float* row = staged ? s_val + ix * L + 4 * l : val + (int64_t)ix * L + 4 * l;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          if (l + k * G < V) {
+            const float4 x = *reinterpret_cast<const float4*>(row + 4 * k * G);
+            acc[k].x = __fmaf_rn(w, x.x, acc[k].x);
+            acc[k].y = __fmaf_rn(w, x.y, acc[k].y);
+            acc[k].z = __fmaf_rn(w, x.z, acc[k].z);
+            acc[k].w = __fmaf_rn(w, x.w, acc[k].w);
+          }
+        }
+      }
       float en[16];
       float best = INFINITY;
       int arg = 0x7fffffff;
@@ -121,23 +153,10 @@ readout_tiled_kernel(const float* __restrict__ val, int L, int64_t n, int d1,
       for (int k = 0; k < 4; k++) {
         const int v = l + k * G;
         if (v < V) {
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-          for (int j = 0; j < d1; j++) {
-            const float w = s_w[r * d1 + j];
-            const int ix = s_idx[r * d1 + j];
-            const float4 x = staged ? *reinterpret_cast<const float4*>(s_val + ix * L + 4 * v)
-                                    : *reinterpret_cast<const float4*>(val + (int64_t)ix * L + 4 * v);
-            acc.x = __fmaf_rn(w, x.x, acc.x);
-            acc.y = __fmaf_rn(w, x.y, acc.y);
-            acc.z = __fmaf_rn(w, x.z, acc.z);
-            acc.w = __fmaf_rn(w, x.w, acc.w);
-          }
-          const float4 pp = *reinterpret_cast<const float4*>(p + px * L + 4 * v);
-          const float4 ee = *reinterpret_cast<const float4*>(e0 + px * L + 4 * v);
-          en[4 * k] = __fadd_rn(ee.x, __fsub_rn(acc.x, pp.x));
-          en[4 * k + 1] = __fadd_rn(ee.y, __fsub_rn(acc.y, pp.y));
-          en[4 * k + 2] = __fadd_rn(ee.z, __fsub_rn(acc.z, pp.z));
-          en[4 * k + 3] = __fadd_rn(ee.w, __fsub_rn(acc.w, pp.w));
+          en[4 * k] = __fadd_rn(ee[k].x, __fsub_rn(acc[k].x, pp[k].x));
+          en[4 * k + 1] = __fadd_rn(ee[k].y, __fsub_rn(acc[k].y, pp[k].y));
+          en[4 * k + 2] = __fadd_rn(ee[k].z, __fsub_rn(acc[k].z, pp[k].z));
+          en[4 * k + 3] = __fadd_rn(ee[k].w, __fsub_rn(acc[k].w, pp[k].w));
 #pragma unroll
           for (int c = 0; c < 4; c++)     // ascending label index: the first minimum wins
             if (en[4 * k + c] < best) { best = en[4 * k + c]; arg = 4 * v + c; }
@@ -261,7 +280,7 @@ int readout_tiled(Lattice* L, const float* val, int labels, float denom, const f
     set_last_error("readout_tiled: d + 1 = %d too large", d1);
     return PL_ERR_INVALID;
   }
-  PL_LAUNCH(readout_tiled_kernel, (unsigned)L->ntiles, kThreads, smem, st, val, labels, L->n, d1,
+  PL_LAUNCH_PDL(readout_tiled_kernel, (unsigned)L->ntiles, kThreads, smem, st, val, labels, L->n, d1,
             L->loc, L->bary, L->vid, L->useg, L->tile_off, L->tile_U, 1.0f / denom, p, e0,
             label_values, depth, label_out, G, (int)stage);
   return PL_OK;

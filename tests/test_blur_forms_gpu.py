@@ -53,8 +53,8 @@ def _sparse(n, C, seed):
 
 
 @pytest.mark.parametrize("h,w,kw", [(120, 160, {}), (32, 48, {"s_ij": 0.02, "s_rgb": 0.2, "noise": 0.3}),
-                                     # M/n ~ 3.7: 64 channels exceed the flow form's one item per thread, so
-                                     # consecutive calls on this lattice alternate between the two forms
+                                     # M/n ~ 3.7: 64 channels take the flow form with two items per thread,
+                                     # fewer channels the one-item form
                                      (48, 64, {"s_ij": 0.02, "s_rgb": 0.2, "noise": 0.3})])
 def test_flow_and_barrier_blur_are_bit_identical(native, h, w, kw):
     feats = torch.from_numpy(_features(h, w, **kw)).cuda()
