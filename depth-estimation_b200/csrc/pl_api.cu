@@ -85,7 +85,7 @@ static void lattice_release(Lattice* L, cudaStream_t st) {
   dev_free(L->rec_splat, st);
   dev_free(L->val[0], st);
   dev_free(L->val[1], st);
-  dev_free(L->flow, st);
+  if (!(getenv("PL_FLOW_DBG") && (atoi(getenv("PL_FLOW_DBG")) & 2))) dev_free(L->flow, st);   // TEMPORARY
   if (L->max_U_ev != nullptr) cudaEventDestroy(L->max_U_ev);
   delete L;
 }

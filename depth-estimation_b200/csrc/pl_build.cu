@@ -378,10 +378,7 @@ scan_chunks_kernel(uint32_t* __restrict__ chunk_count, uint32_t nchunks, uint32_
 template <int D>
 __global__ void __launch_bounds__(kScanThreads)
 assign_kernel(const unsigned long long* __restrict__ table, const int32_t* __restrict__ slot,
-              uint64_t E, const uint32_t* __restrict__ chunk_offset,
-              const int16_t* __restrict__ greedy, const int8_t* __restrict__ rank,
-              int32_t* __restrict__ slot_vid, int16_t* __restrict__ vkeys,
-              uint32_t* __restrict__ first_e, int32_t* __restrict__ vslot) {
+              uint64_t E, const uint32_t* __restrict__ chunk_offset, int32_t* __restrict__ slot_vid) {
   __shared__ uint32_t warp_cnt[kScanThreads / 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint64_t base = (uint64_t)blockIdx.x * kScanChunk;
@@ -403,15 +400,6 @@ assign_kernel(const unsigned long long* __restrict__ table, const int32_t* __res
     if (first) {
       const uint32_t v = running + before + __popc(bal & ((1u << lane) - 1u));
       slot_vid[slot[e]] = (int32_t)v;
-      if (first_e != nullptr) {   // growth-quirk replay: where and when each vertex was created
-        first_e[v] = (uint32_t)e;
-        vslot[v] = slot[e];
-      }
-      int16_t key[D];
-      const uint64_t p = e / (D + 1);
-      load_key<D>(greedy, rank, (int64_t)p, (int)(e - p * (D + 1)), key);
-#pragma unroll
-      for (int i = 0; i < D; i++) vkeys[(uint64_t)v * D + i] = key[i];
     }
     running += total;
     __syncthreads();
@@ -425,6 +413,40 @@ gather_kernel(int32_t* __restrict__ slot_then_vid, const int32_t* __restrict__ s
   for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E;
        e += (uint64_t)gridDim.x * blockDim.x)
     slot_then_vid[e] = slot_vid[slot_then_vid[e]];
+}
+
+// 4b. per vertex: its key (and, for the growth-quirk replay, where and when it was created).  One
+// thread per table slot: an occupied slot holds the entry id of its key's first touch, and
+// assign_kernel has given it the vertex id.  This is the only build kernel in front of the neighbour
+// table whose OUTPUT is sized by M, so it is the first one that has to wait for M on the host:
+// assign and gather are queued before the host blocks.
+template <int D>
+__global__ void __launch_bounds__(256)
+keys_kernel(const unsigned long long* __restrict__ table, const int32_t* __restrict__ slot_vid,
+            uint64_t cap, const int16_t* __restrict__ greedy, const int8_t* __restrict__ rank,
+            int16_t* __restrict__ vkeys, uint32_t* __restrict__ first_e, int32_t* __restrict__ vslot) {
+  const ulonglong2* t2 = reinterpret_cast<const ulonglong2*>(table);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < cap / 2;
+       i += (uint64_t)gridDim.x * blockDim.x) {
+    const ulonglong2 pair = t2[i];
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      const unsigned long long cur = k == 0 ? pair.x : pair.y;
+      if (cur == kEmpty) continue;
+      const uint64_t h = 2 * i + k;
+      const uint32_t e = (uint32_t)cur;
+      const int32_t v = slot_vid[h];
+      if (first_e != nullptr) {
+        first_e[v] = e;
+        vslot[v] = (int32_t)h;
+      }
+      int16_t key[D];
+      const uint32_t p = e / (D + 1);
+      load_key<D>(greedy, rank, (int64_t)p, (int)(e - p * (D + 1)), key);
+#pragma unroll
+      for (int j = 0; j < D; j++) vkeys[(uint64_t)v * D + j] = key[j];
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -917,7 +939,17 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
 
   uint64_t cap = pow2_ceil(E + E / 4 + 1024);
   unsigned long long* table = nullptr;
-  uint32_t host_res[2] = {0, 0};
+  int32_t* slot_vid = nullptr;
+  // M and the overflow flag come back through a pinned slot, and the host waits on an event recorded
+  // right behind that copy: assign + gather, which need neither, are queued before the host blocks, so
+  // the device still has work when the host resumes (a stream synchronise here left it idle for
+  // ~25 us per frame, and the launches after it could not catch up before the first filter call)
+  uint32_t pageable_res[2] = {0, 0};
+  uint32_t* host_res = reinterpret_cast<uint32_t*>(pinned_slot());
+  const bool pinned = host_res != nullptr;
+  if (!pinned) host_res = pageable_res;
+  if (pinned && L->max_U_ev == nullptr)
+    PL_CUDA(cudaEventCreateWithFlags(&L->max_U_ev, cudaEventDisableTiming));
   for (int attempt = 0;; attempt++) {
     if (cap > (1ull << 31)) {
       dev_free(chunk_count, st);
@@ -925,6 +957,7 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
       return PL_ERR_OVERFLOW;
     }
     PL_TRY(dev_alloc((void**)&table, sizeof(unsigned long long) * cap, st));
+    PL_TRY(dev_alloc((void**)&slot_vid, sizeof(int32_t) * cap, st));
     PL_CUDA(cudaMemsetAsync(table, 0xFF, sizeof(unsigned long long) * cap, st));
     PL_CUDA(cudaMemsetAsync(total_dev, 0, 2 * sizeof(uint32_t), st));
     trace.point("alloc + clear hash table");
@@ -932,11 +965,21 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
               table, (uint32_t)(cap - 1), L->vid, overflow_dev);
     PL_LAUNCH(count_first_kernel, nchunks, kScanThreads, 0, st, table, L->vid, E, chunk_count);
     PL_LAUNCH(scan_chunks_kernel, 1, 1024, 0, st, chunk_count, nchunks, total_dev);
-    PL_CUDA(cudaMemcpyAsync(host_res, total_dev, sizeof(host_res), cudaMemcpyDeviceToHost, st));
-    PL_CUDA(cudaStreamSynchronize(st));
+    PL_CUDA(cudaMemcpyAsync(host_res, total_dev, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    if (pinned) PL_CUDA(cudaEventRecord(L->max_U_ev, st));
+    // after an overflow these two run on an incomplete table: every slot index is still inside the
+    // table, their output is discarded, and insert_kernel rewrites L->vid on the retry
+    PL_LAUNCH((assign_kernel<D>), nchunks, kScanThreads, 0, st, table, L->vid, E, chunk_count, slot_vid);
+    PL_LAUNCH(gather_kernel, grid_for(E, 256, 8), 256, 0, st, L->vid, slot_vid, E);
+    if (pinned)
+      PL_CUDA(cudaEventSynchronize(L->max_U_ev));
+    else
+      PL_CUDA(cudaStreamSynchronize(st));
     if (host_res[1] == 0) break;
     dev_free(table, st);
+    dev_free(slot_vid, st);
     table = nullptr;
+    slot_vid = nullptr;
     cap *= 2;
     if (attempt >= 4) {
       dev_free(chunk_count, st);
@@ -946,10 +989,8 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
   }
   const int64_t M = (int64_t)host_res[0];
   L->M = M;
-  trace.point("insert + count + scan + sync");
+  trace.point("insert + count + scan + assign + gather queued, M read back");
 
-  int32_t* slot_vid = nullptr;
-  PL_TRY(dev_alloc((void**)&slot_vid, sizeof(int32_t) * cap, st));
   // the reference's table only ever grows once it holds 2^14 - 1 vertices (permutohedral.h:36,62)
   const bool quirk = (L->flags & PL_BUILD_REF_GROW_QUIRK) != 0 && M >= (1 << 14) - 1;
   int16_t* vkeys_clean = nullptr;
@@ -960,9 +1001,8 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
     PL_TRY(dev_alloc((void**)&first_e, sizeof(uint32_t) * (size_t)M, st));
     PL_TRY(dev_alloc((void**)&vslot, sizeof(int32_t) * (size_t)M, st));
   }
-  PL_LAUNCH((assign_kernel<D>), nchunks, kScanThreads, 0, st, table, L->vid, E, chunk_count,
-            L->greedy, L->rank, slot_vid, vkeys_clean, first_e, vslot);
-  PL_LAUNCH(gather_kernel, grid_for(E, 256, 8), 256, 0, st, L->vid, slot_vid, E);
+  PL_LAUNCH((keys_kernel<D>), grid_for(cap / 2, 256, 8), 256, 0, st, table, slot_vid, cap, L->greedy, L->rank,
+            vkeys_clean, first_e, vslot);
   int64_t Mf = M;
   if (quirk) {
     GrowQuirk* qd = nullptr;

@@ -199,6 +199,7 @@ struct GuideSrc {
 int lattice_build(Lattice* L, const float* ref, cudaStream_t st, const GuideSrc* guide = nullptr);
 // tile-local view + tiled kernels (pl_tiles.cu)
 int lattice_build_tiles(Lattice* L, cudaStream_t st);
+int* pinned_slot();   // pl_tiles.cu: two pinned ints for a small device -> host result, nullptr if unavailable
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
                 cudaStream_t st, const float* rowscale = nullptr, int64_t rs_stride = 0, int J = 1);
 int splat_sorted(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val, cudaStream_t st);

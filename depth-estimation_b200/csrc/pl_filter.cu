@@ -815,12 +815,19 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
         dev_free(L->flow, st);
         L->flow = nullptr;
         L->flow_floats = 0;
-        PL_TRY(dev_alloc((void**)&L->flow, sizeof(float) * (size_t)per * 10, st));
+        static const int dbg = getenv("PL_FLOW_DBG") ? atoi(getenv("PL_FLOW_DBG")) : 0;   // TEMPORARY
+        static float* dbg_buf = nullptr;
+        if (dbg & 2) {
+          if (dbg_buf == nullptr) cudaMalloc((void**)&dbg_buf, 64 << 20);
+          L->flow = dbg_buf;
+        } else {
+          PL_TRY(dev_alloc((void**)&L->flow, sizeof(float) * (size_t)per * 10, st));
+        }
         L->flow_floats = per;
         L->flow_set = 0;
         L->flow_dirty[0] = 0;
         L->flow_dirty[1] = per;     // uninitialised memory: to be refilled in full
-        PL_CUDA(cudaMemsetAsync(L->flow, 0xFF, sizeof(float) * (size_t)per * 5, st));
+        if (!(dbg & 1)) PL_CUDA(cudaMemsetAsync(L->flow, 0xFF, sizeof(float) * (size_t)per * 5, st));
       }
       const int s_use = L->flow_set, s_fill = 1 - s_use;
       const size_t stride = (size_t)L->flow_floats;

@@ -383,8 +383,11 @@ int pow2_ceil_i(int x) {
 
 namespace {
 
-// pinned slots the devices report max U into (a ring: a stale slot can only cost speed, the
-// kernels decide staged / unstaged per tile from the tile's own U)
+}  // namespace
+
+// pinned two-int slots for small device -> host results: max U of the tile build (read lazily: a slot
+// recycled 2048 lattices later can only cost speed, the kernels decide staged / unstaged per tile from
+// the tile's own U) and M of the lattice build (read before the build returns)
 int* pinned_slot() {
   static int* ring = nullptr;
   static std::once_flag once;
@@ -399,6 +402,8 @@ int* pinned_slot() {
   // two ints per lattice: {sum of U over the tiles, max U}
   return ring == nullptr ? nullptr : ring + (next.fetch_add(2, std::memory_order_relaxed) % kSlots);
 }
+
+namespace {
 
 int tiles_max_u(Lattice* L, cudaStream_t st) {
   int* d_max = L->tile_off + 2 * L->ntiles;     // {useg cursor = sum of U, max U}

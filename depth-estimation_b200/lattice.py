@@ -19,6 +19,26 @@ import torch
 from . import _native as N
 
 
+_MU_T = {}       # id(mu) -> (mu, version, transposed copy); holds mu itself, so its id cannot be reused
+_MU_T_MAX = 4
+
+
+def _transposed(mu):
+    """``mu.t().contiguous()`` for the C ABI (which takes Mu^T), remembered per compatibility tensor:
+    a streaming loop passes the same Mu every frame, and the transposition is a kernel launch plus
+    host time that sits on the critical path between the lattice build and the first iteration.
+    The entry keeps a reference to ``mu`` (the key is its identity, the in-place version counter
+    invalidates it), so a recycled address or id can never match."""
+    ent = _MU_T.get(id(mu))
+    if ent is not None and ent[0] is mu and ent[1] == mu._version:
+        return ent[2]
+    mu_t = mu.detach().t().contiguous()
+    if len(_MU_T) >= _MU_T_MAX:
+        _MU_T.pop(next(iter(_MU_T)))
+    _MU_T[id(mu)] = (mu, mu._version, mu_t)
+    return mu_t
+
+
 class PermutohedralLattice:
     """Cached lattice for one feature matrix ``ref[n, d]`` (CUDA, fp32).
 
@@ -161,7 +181,7 @@ class PermutohedralLattice:
         N.require_cuda_f32(mu, "mu", 2)
         if tuple(mu.shape) != (L, L):
             raise ValueError(f"mu must be [{L}, {L}]")
-        mu_t = mu.t().contiguous()
+        mu_t = _transposed(mu)
         out = torch.empty_like(e0)
         work = torch.empty_like(e0)
         flags = ((N.PL_APPLY_EXACT_SLICE if exact_slice else 0) | (N.PL_APPLY_FLAT_KERNELS if flat else 0)
@@ -186,7 +206,7 @@ class PermutohedralLattice:
         N.require_cuda_f32(mu, "mu", 2)
         if tuple(mu.shape) != (L, L):
             raise ValueError(f"mu must be [{L}, {L}]")
-        mu_t = mu.t().contiguous()
+        mu_t = _transposed(mu)
         if labels is not None:
             N.require_cuda_f32(labels, "labels")
             labels = labels.reshape(-1).contiguous()
