@@ -932,10 +932,8 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
 
   trace.point("elevate");
   const uint32_t nchunks = ceil_div_u(E, kScanChunk);
-  uint32_t* chunk_count = nullptr;  // [nchunks] + total + overflow flag
-  PL_TRY(dev_alloc((void**)&chunk_count, sizeof(uint32_t) * ((size_t)nchunks + 2), st));
-  uint32_t* total_dev = chunk_count + nchunks;
-  int* overflow_dev = (int*)(chunk_count + nchunks + 1);
+  uint32_t* chunk_count = nullptr;  // [nchunks]
+  PL_TRY(dev_alloc((void**)&chunk_count, sizeof(uint32_t) * (size_t)nchunks, st));
 
   uint64_t cap = pow2_ceil(E + E / 4 + 1024);
   unsigned long long* table = nullptr;
@@ -956,10 +954,13 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
       set_last_error("hash table would need %llu slots", (unsigned long long)cap);
       return PL_ERR_OVERFLOW;
     }
-    PL_TRY(dev_alloc((void**)&table, sizeof(unsigned long long) * cap, st));
+    // one more slot behind the table holds {vertex count, overflow flag}, so that the clear of the table
+    // covers them: the count is written by the scan, the flag reads 0xFFFFFFFF until an insert overflows
+    PL_TRY(dev_alloc((void**)&table, sizeof(unsigned long long) * (cap + 1), st));
     PL_TRY(dev_alloc((void**)&slot_vid, sizeof(int32_t) * cap, st));
-    PL_CUDA(cudaMemsetAsync(table, 0xFF, sizeof(unsigned long long) * cap, st));
-    PL_CUDA(cudaMemsetAsync(total_dev, 0, 2 * sizeof(uint32_t), st));
+    uint32_t* total_dev = reinterpret_cast<uint32_t*>(table + cap);
+    int* overflow_dev = reinterpret_cast<int*>(total_dev + 1);
+    PL_CUDA(cudaMemsetAsync(table, 0xFF, sizeof(unsigned long long) * (cap + 1), st));
     trace.point("alloc + clear hash table");
     PL_LAUNCH((insert_kernel<D>), grid_for((uint64_t)n, 256, 8), 256, 0, st, L->greedy, L->rank, n,
               table, (uint32_t)(cap - 1), L->vid, overflow_dev);
@@ -975,7 +976,7 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
       PL_CUDA(cudaEventSynchronize(L->max_U_ev));
     else
       PL_CUDA(cudaStreamSynchronize(st));
-    if (host_res[1] == 0) break;
+    if (host_res[1] == 0xFFFFFFFFu) break;     // no insert overflowed
     dev_free(table, st);
     dev_free(slot_vid, st);
     table = nullptr;

@@ -220,6 +220,11 @@ int lattice_apply(Lattice* L, const float* src, int64_t src_stride, float* dst, 
                   uint32_t flags, cudaStream_t st);
 int lattice_workspace(Lattice* L, int Cc, cudaStream_t st, bool third = false);
 bool lattice_blur_is_flow(const Lattice* L, int Cc);
+int lattice_splat_buffers(Lattice* L, int Cc, cudaStream_t st, float** cur, float** nxt);
+// scratch of the barrier-free blur for Cc channels.  If it had to be (re)allocated, its first set must be
+// filled with 0xFF bytes before the next blur: with fill_ptr == nullptr that is done here by a memset,
+// else the region is handed to the caller (*fill_bytes == 0: nothing to fill).
+int lattice_flow_prepare(Lattice* L, int Cc, cudaStream_t st, void** fill_ptr, size_t* fill_bytes);
 // `zero_other`: leave a zeroed buffer behind for the next splat -- the one of cur / nxt that does not
 // hold the result, unless `zeroed` is given and comes back non-null: then it names the buffer that was
 // zeroed instead (`spare`, a third buffer of the same shape that nothing reads while the blur runs).
@@ -245,7 +250,7 @@ int tc_timeouts();
 bool mf_ws_supported(const Lattice* L, int labels);
 int mf_ws_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
                     const float* p_prev, float* p_next, const float* mu_canon, float scale,
-                    int labels, cudaStream_t st);
+                    int labels, cudaStream_t st, void* fill = nullptr, size_t fill_bytes = 0);
 int ws_timeouts();
 // softmax + compatibility for large label counts / label shards on tcgen05 (pl_compat_tc.cu)
 bool compat_tc_supported(int L, int N, int block_w);

@@ -647,11 +647,10 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
   const int D1 = L->d + 1;
   const int64_t M = L->M, n = L->n;
   const size_t row = sizeof(float) * (size_t)Cc;
-  float* cur = L->val[0];
-  float* nxt = L->val[1];
   // zero the accumulation buffer (incl. row M) and the other buffer's row M
-  PL_CUDA(cudaMemsetAsync(cur, 0, row * (size_t)(M + 1), st));
-  PL_CUDA(cudaMemsetAsync(nxt + (size_t)M * Cc, 0, row, st));
+  float* cur = nullptr;
+  float* nxt = nullptr;
+  PL_TRY(lattice_splat_buffers(L, Cc, st, &cur, &nxt));
 
   const uint64_t pix_items = (uint64_t)n * (uint64_t)(Cc / VEC);
   const uint64_t vtx_items = (uint64_t)M * (uint64_t)(Cc / VEC);
@@ -722,13 +721,12 @@ int apply_chunk(Lattice* L, const float* src, int64_t src_stride, float* dst, in
 int lattice_workspace(Lattice* L, int Cc, cudaStream_t st, bool third) {
   const int64_t need = (L->M + 1) * (int64_t)Cc;
   if (L->ws_floats < need) {
-    for (int k = 0; k < 3; k++) {
-      if (L->val[k]) dev_free(L->val[k], st);
-      L->val[k] = nullptr;
-    }
+    // val[1] and val[0] share one block (val[1] first): see lattice_splat_buffers
+    if (L->val[1]) dev_free(L->val[1], st);
+    if (L->val[2]) dev_free(L->val[2], st);
+    L->val[0] = L->val[1] = L->val[2] = nullptr;
     L->ws_floats = 0;
-    PL_TRY(dev_alloc((void**)&L->val[0], sizeof(float) * (size_t)need, st));
-    PL_TRY(dev_alloc((void**)&L->val[1], sizeof(float) * (size_t)need, st));
+    PL_TRY(dev_alloc((void**)&L->val[1], sizeof(float) * (size_t)need * 2, st));
     L->ws_floats = need;
   }
   if (third && L->val[2] == nullptr)
@@ -736,9 +734,18 @@ int lattice_workspace(Lattice* L, int Cc, cudaStream_t st, bool third) {
   return PL_OK;
 }
 
-// whether lattice_blur takes the barrier-free form for this shape (the mean-field loop then rotates
-// three value buffers so that the next splat target is zeroed inside the blur kernel).
-// PL_BLUR_FORM=reg (read per call: tests/test_blur_forms_gpu.py flips it) keeps the grid-barrier forms.
+// The two value buffers for a filter with Cc channels, ready for a splat into *cur: *cur is all zero
+// (rows 0..M) and row M of *nxt is zero (absent blur neighbours read it).  *cur is placed right behind
+// *nxt's (M+1) x Cc floats, so that ONE memset covers row M of *nxt and all of *cur.
+int lattice_splat_buffers(Lattice* L, int Cc, cudaStream_t st, float** cur, float** nxt) {
+  const size_t rowf = (size_t)Cc, rows = (size_t)L->M + 1;
+  L->val[0] = L->val[1] + rows * rowf;
+  *nxt = L->val[1];
+  *cur = L->val[0];
+  PL_CUDA(cudaMemsetAsync(*nxt + (size_t)L->M * rowf, 0, sizeof(float) * rowf * (rows + 1), st));
+  return PL_OK;
+}
+
 // items per thread of the barrier-free form for this shape; 0: not applicable
 static int blur_flow_items(const Lattice* L, int Cc) {
   const char* form = getenv("PL_BLUR_FORM");
@@ -751,6 +758,28 @@ static int blur_flow_items(const Lattice* L, int Cc) {
   return 0;
 }
 bool lattice_blur_is_flow(const Lattice* L, int Cc) { return blur_flow_items(L, Cc) > 0; }
+
+int lattice_flow_prepare(Lattice* L, int Cc, cudaStream_t st, void** fill_ptr, size_t* fill_bytes) {
+  if (fill_bytes != nullptr) *fill_bytes = 0;
+  const int64_t per = L->M * (int64_t)Cc;
+  if (L->flow_floats >= per) return PL_OK;
+  dev_free(L->flow, st);
+  L->flow = nullptr;
+  L->flow_floats = 0;
+  PL_TRY(dev_alloc((void**)&L->flow, sizeof(float) * (size_t)per * 10, st));
+  L->flow_floats = per;
+  L->flow_set = 0;
+  L->flow_dirty[0] = 0;
+  L->flow_dirty[1] = per;     // uninitialised memory: to be refilled in full
+  const size_t bytes = sizeof(float) * (size_t)per * 5;
+  if (fill_ptr != nullptr && fill_bytes != nullptr) {
+    *fill_ptr = L->flow;
+    *fill_bytes = bytes;
+  } else {
+    PL_CUDA(cudaMemsetAsync(L->flow, 0xFF, bytes, st));
+  }
+  return PL_OK;
+}
 
 // d+1 Jacobi passes starting from `cur` (scratch `nxt`); *out = buffer holding the result.
 // Both buffers must have a zero row M.  Cc % 4 == 0.
@@ -811,24 +840,7 @@ int lattice_blur(Lattice* L, float* cur, float* nxt, int Cc, cudaStream_t st, fl
     if (flow_occ[devi] >= 2) {
       const int64_t per = M * (int64_t)Cc;
       const bool fresh = L->flow_floats < per;   // a memset sits in front of this launch
-      if (fresh) {
-        dev_free(L->flow, st);
-        L->flow = nullptr;
-        L->flow_floats = 0;
-        static const int dbg = getenv("PL_FLOW_DBG") ? atoi(getenv("PL_FLOW_DBG")) : 0;   // TEMPORARY
-        static float* dbg_buf = nullptr;
-        if (dbg & 2) {
-          if (dbg_buf == nullptr) cudaMalloc((void**)&dbg_buf, 64 << 20);
-          L->flow = dbg_buf;
-        } else {
-          PL_TRY(dev_alloc((void**)&L->flow, sizeof(float) * (size_t)per * 10, st));
-        }
-        L->flow_floats = per;
-        L->flow_set = 0;
-        L->flow_dirty[0] = 0;
-        L->flow_dirty[1] = per;     // uninitialised memory: to be refilled in full
-        if (!(dbg & 1)) PL_CUDA(cudaMemsetAsync(L->flow, 0xFF, sizeof(float) * (size_t)per * 5, st));
-      }
+      PL_TRY(lattice_flow_prepare(L, Cc, st, nullptr, nullptr));
       const int s_use = L->flow_set, s_fill = 1 - s_use;
       const size_t stride = (size_t)L->flow_floats;
       float* use = L->flow + (size_t)s_use * 5 * stride;
@@ -943,11 +955,9 @@ int lattice_apply_dot(Lattice* L, const float* src, int64_t src_stride, int C, c
     return PL_ERR_INVALID;
   }
   PL_TRY(lattice_workspace(L, C, st));
-  float* cur = L->val[0];
-  float* nxt = L->val[1];
-  const size_t row = sizeof(float) * (size_t)C;
-  PL_CUDA(cudaMemsetAsync(cur, 0, row * (size_t)rows, st));
-  PL_CUDA(cudaMemsetAsync(nxt + (size_t)L->M * C, 0, row, st));
+  float* cur = nullptr;
+  float* nxt = nullptr;
+  PL_TRY(lattice_splat_buffers(L, C, st, &cur, &nxt));
   PL_TRY(splat_tiled(L, src, src_stride, Cs, cur, st, rowscale, rs_stride, J));
   float* res = nullptr;
   PL_TRY(lattice_blur(L, cur, nxt, C, st, &res));

@@ -73,6 +73,8 @@ struct WsArgs {
   const int2* useg;
   const int* tile_off;
   const int* tile_U;
+  uint4* fill;          // first iteration only: region to fill with 0xFF bytes (the blur's sentinel scratch)
+  uint32_t fill_n16;    // its size in 16-byte units
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float2 a, float2 b) {
@@ -125,6 +127,10 @@ __global__ void __launch_bounds__(kThreads, 1) mf_ws_kernel(const WsArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t stride = gridDim.x;
   const int64_t tile0 = blockIdx.x;
+  if (FIRST && a.fill_n16 > 0) {   // fire-and-forget: nothing in this kernel reads it
+    const uint4 s4 = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+    for (uint32_t i = blockIdx.x * kThreads + tid; i < a.fill_n16; i += gridDim.x * kThreads) a.fill[i] = s4;
+  }
   if (tile0 >= a.ntiles) return;
   const uint32_t my_tiles = (uint32_t)((a.ntiles - tile0 + stride - 1) / stride);
 
@@ -475,8 +481,14 @@ bool mf_ws_supported(const Lattice* L, int labels) {
 // One iteration (same contract as mf_tc_iteration; mu_canon from mf_tc_prepare_mu).
 int mf_ws_iteration(Lattice* L, bool first, const float* val_in, float* val_out, const float* e0,
                     const float* p_prev, float* p_next, const float* mu_canon, float scale,
-                    int labels, cudaStream_t st) {
+                    int labels, cudaStream_t st, void* fill, size_t fill_bytes) {
   WsArgs a = {};
+  if (first && fill != nullptr && fill_bytes % 16 == 0 && fill_bytes / 16 < 0xffffffffull) {
+    a.fill = reinterpret_cast<uint4*>(fill);
+    a.fill_n16 = (uint32_t)(fill_bytes / 16);
+  } else if (fill != nullptr && fill_bytes > 0) {
+    PL_CUDA(cudaMemsetAsync(fill, 0xFF, fill_bytes, st));
+  }
   a.val_in = val_in; a.val_out = val_out; a.e0 = e0; a.p_prev = p_prev; a.p_next = p_next;
   a.mu_canon = mu_canon; a.scale = scale; a.n = L->n; a.ntiles = L->ntiles;
   a.inv_denom = 1.0f / (1 + powf(2, -L->d));

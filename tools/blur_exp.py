@@ -1,4 +1,4 @@
-"""A/B of the small-lattice blur forms (PL_BLUR_EXP, read per call while the experiment lasts):
+"""A/B of the small-lattice blur forms (PL_BLUR_FORM, read per call: "reg" = grid-barrier form, "flow" = default):
 bitwise comparison of a filter apply and of a 5-iteration mean-field frame, then device time per frame.
 
     python tools/blur_exp.py [H W L variant]
@@ -14,7 +14,7 @@ synthetic = importlib.import_module("depth_estimation_b200.synthetic")
 h, w, L, variant = 500, 740, 64, "default"
 if len(sys.argv) > 4:
     h, w, L, variant = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4]
-modes = os.environ.get("BLUR_MODES", "0,3").split(",")
+modes = os.environ.get("BLUR_MODES", "reg,flow").split(",")
 dev = torch.device("cuda", 0)
 feats = torch.from_numpy(U.features(h, w, variant)).to(dev)
 g = torch.Generator(device=dev).manual_seed(1)
@@ -33,7 +33,7 @@ def frame():
 
 res = {}
 for m in modes:
-    os.environ["PL_BLUR_EXP"] = m
+    os.environ["PL_BLUR_FORM"] = m
     f = lat.filter(src).clone()
     f2 = lat.filter(src).clone()          # second call: buffers in the state the first one left
     e = frame().clone()
@@ -54,7 +54,7 @@ for m in modes:
 
 for rep in range(2):
     for m in modes:
-        os.environ["PL_BLUR_EXP"] = m
+        os.environ["PL_BLUR_FORM"] = m
         for _ in range(5):
             frame()
         torch.cuda.synchronize()
