@@ -179,6 +179,7 @@ static void lattice_release(Lattice* L, cudaStream_t st) {
   dev_free(L->val[2], st);
   dev_free(L->flow, st);
   if (L->max_U_ev != nullptr) cudaEventDestroy(L->max_U_ev);
+  if (L->aux_ev != nullptr) cudaEventDestroy(L->aux_ev);
   delete L;
 }
 

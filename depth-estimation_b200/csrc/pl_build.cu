@@ -946,8 +946,6 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
   uint32_t* host_res = reinterpret_cast<uint32_t*>(pinned_slot());
   const bool pinned = host_res != nullptr;
   if (!pinned) host_res = pageable_res;
-  if (pinned && L->max_U_ev == nullptr)
-    PL_CUDA(cudaEventCreateWithFlags(&L->max_U_ev, cudaEventDisableTiming));
   for (int attempt = 0;; attempt++) {
     if (cap > (1ull << 31)) {
       dev_free(chunk_count, st);
@@ -966,8 +964,10 @@ int build_impl(Lattice* L, const float* ref, const GuideSrc& gs, cudaStream_t st
               table, (uint32_t)(cap - 1), L->vid, overflow_dev);
     PL_LAUNCH(count_first_kernel, nchunks, kScanThreads, 0, st, table, L->vid, E, chunk_count);
     PL_LAUNCH(scan_chunks_kernel, 1, 1024, 0, st, chunk_count, nchunks, total_dev);
-    PL_CUDA(cudaMemcpyAsync(host_res, total_dev, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    if (pinned) PL_CUDA(cudaEventRecord(L->max_U_ev, st));
+    if (pinned)
+      PL_TRY(readback_small(L, host_res, total_dev, 2 * sizeof(uint32_t), st));
+    else
+      PL_CUDA(cudaMemcpyAsync(host_res, total_dev, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     // after an overflow these two run on an incomplete table: every slot index is still inside the
     // table, their output is discarded, and insert_kernel rewrites L->vid on the retry
     PL_LAUNCH((assign_kernel<D>), nchunks, kScanThreads, 0, st, table, L->vid, E, chunk_count, slot_vid);

@@ -175,6 +175,7 @@ struct Lattice {
   int mean_U = 0;              // mean distinct-vertex count per tile (same read-back)
   int* h_max_U = nullptr;
   cudaEvent_t max_U_ev = nullptr;
+  cudaEvent_t aux_ev = nullptr;     // marks the point of the caller's stream a side-stream copy has to wait for
   // grow-only value workspace: two ping-pong buffers of (M+1) x ws_C floats, and a third one for the
   // mean-field loop's buffer rotation on small lattices (lattice_workspace(..., third = true))
   float* val[3] = {nullptr, nullptr, nullptr};
@@ -199,6 +200,11 @@ struct GuideSrc {
 int lattice_build(Lattice* L, const float* ref, cudaStream_t st, const GuideSrc* guide = nullptr);
 // tile-local view + tiled kernels (pl_tiles.cu)
 int lattice_build_tiles(Lattice* L, cudaStream_t st);
+// Small device -> host results (M of the build, max U of the tile build) are copied on a per-device side
+// stream behind an event of the caller's stream, so the copy engine works beside the next kernels instead
+// of between them (each in-stream copy cost ~9 us of an 820 us frame: the copy plus two gaps).
+// Records L->max_U_ev behind the copy; the host waits on that event when it needs the value.
+int readback_small(Lattice* L, void* host_dst, const void* dev_src, size_t bytes, cudaStream_t st);
 int* pinned_slot();   // pl_tiles.cu: two pinned ints for a small device -> host result, nullptr if unavailable
 int splat_tiled(Lattice* L, const float* src, int64_t src_stride, int Cc, float* val,
                 cudaStream_t st, const float* rowscale = nullptr, int64_t rs_stride = 0, int J = 1);

@@ -405,6 +405,34 @@ int* pinned_slot() {
 
 namespace {
 
+}  // namespace
+
+int readback_small(Lattice* L, void* host_dst, const void* dev_src, size_t bytes, cudaStream_t st) {
+  static cudaStream_t side[64] = {};
+  static std::mutex mu;
+  int dev = 0;
+  PL_CUDA(cudaGetDevice(&dev));
+  cudaStream_t ss = nullptr;
+  if (dev >= 0 && dev < 64) {
+    std::lock_guard<std::mutex> lock(mu);
+    if (side[dev] == nullptr) PL_CUDA(cudaStreamCreateWithFlags(&side[dev], cudaStreamNonBlocking));
+    ss = side[dev];
+  }
+  if (L->max_U_ev == nullptr) PL_CUDA(cudaEventCreateWithFlags(&L->max_U_ev, cudaEventDisableTiming));
+  if (ss == nullptr) {   // no side stream: in the caller's stream
+    PL_CUDA(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, st));
+    PL_CUDA(cudaEventRecord(L->max_U_ev, st));
+    return PL_OK;
+  }
+  if (L->aux_ev == nullptr) PL_CUDA(cudaEventCreateWithFlags(&L->aux_ev, cudaEventDisableTiming));
+  PL_CUDA(cudaEventRecord(L->aux_ev, st));
+  PL_CUDA(cudaStreamWaitEvent(ss, L->aux_ev, 0));
+  PL_CUDA(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, ss));
+  PL_CUDA(cudaEventRecord(L->max_U_ev, ss));
+  return PL_OK;
+}
+
+namespace {
 int tiles_max_u(Lattice* L, cudaStream_t st) {
   int* d_max = L->tile_off + 2 * L->ntiles;     // {useg cursor = sum of U, max U}
   L->max_U = -1;
@@ -414,10 +442,7 @@ int tiles_max_u(Lattice* L, cudaStream_t st) {
     L->max_U = 1 << 30;   // unknown: largest staging buffer
     return PL_OK;
   }
-  PL_CUDA(cudaMemcpyAsync(L->h_max_U, d_max, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-  if (L->max_U_ev == nullptr) PL_CUDA(cudaEventCreateWithFlags(&L->max_U_ev, cudaEventDisableTiming));
-  PL_CUDA(cudaEventRecord(L->max_U_ev, st));
-  return PL_OK;
+  return readback_small(L, L->h_max_U, d_max, 2 * sizeof(int), st);
 }
 }  // namespace
 

@@ -110,7 +110,13 @@ def test_tsukuba_fixture_pair_to_depth_vs_reference_pipeline(native, cpu_filter)
                                         return_label=True)
     depth, label = depth.cpu().numpy(), label.cpu().numpy()
     assert (label.reshape(-1) == want_e.argmin(1)).mean() > 0.999
-    assert np.abs(depth - want_depth).max() < 2e-2 and np.abs(depth - want_depth).mean() < 1e-3
+    # The soft-argmax amplifies energy differences where two distant disparities tie: 60 repetitions of
+    # this comparison (tools/tsukuba_margins.py) gave label agreement 1.0, mean |error| 3e-7 .. 2e-6 and
+    # E within 3e-6 of its scale every time, but a maximum over the 110 592 pixels anywhere between 0.005
+    # and 0.04 -- one or two bimodal pixels moved by the fp32 summation order of the splat's atomics and
+    # of the fp32 cost volume.  So: the mean, all but the 0.01 % most ambiguous pixels, and a hard cap.
+    err = np.abs(depth - want_depth)
+    assert err.mean() < 1e-4 and np.quantile(err, 0.9999) < 2e-2 and err.max() < 0.25
     # module path on the same frame: CRFasRNN.forward on the flattened guide and the same unaries
     lat = native.PermutohedralLattice(torch.from_numpy(ref).cuda())
     got_e = lat.mean_field(torch.from_numpy(e0).cuda(), torch.from_numpy(mu).cuda(), 5, 1.0).cpu().numpy()
