@@ -1,5 +1,7 @@
 // pl_common.cuh -- shared declarations for libpl_lattice (sm_100a only).
 #pragma once
+#include <atomic>
+#include <vector>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -112,13 +114,24 @@ inline cudaLaunchConfig_t pdl_config(dim3 grid, dim3 block, size_t smem, cudaStr
 
 // Opt-in attributes (cudaFuncSetAttribute) are per DEVICE: a process that drives several GPUs has
 // to set them once on each.  `static PerDeviceOnce once; if (once.need()) { ... }`
+// The flag is also per THREAD: the caller's block has no completion signal, so with a shared flag a
+// second host thread could find it set and launch before the first thread had finished setting the
+// attribute ("invalid argument" for a kernel that needs > 48 KB of shared memory: seen once with the
+// two host threads of the pipelined end-to-end bench).  Setting an attribute twice is harmless.
 struct PerDeviceOnce {
-  bool done[64] = {};
+  uint32_t id;
+  PerDeviceOnce() {
+    static std::atomic<uint32_t> next{0};
+    id = next.fetch_add(1);
+  }
   bool need() {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
-    if (done[dev]) return false;
-    done[dev] = true;
+    thread_local std::vector<uint8_t> seen;     // [id * 64 + device] for the calling thread
+    const size_t k = (size_t)id * 64 + (size_t)dev;
+    if (seen.size() <= k) seen.resize(k + 64, 0);
+    if (seen[k]) return false;
+    seen[k] = 1;
     return true;
   }
 };
