@@ -67,14 +67,24 @@ base_v, base_e = r["value"], r["e2e"]["value"]
 c5 = [c for c in r["extra"]["configs"] if c["workload"].startswith("crf_1920x1080_L128") and c["features"] == "default"]
 c4 = {c["features"]: c for c in r["extra"]["configs"] if c["workload"].startswith("crf_2000x1450_L256")}
 print(f"| 1 | {base_v:.0f} | {base_e:.0f} | {c5[0]['value']:.1f} | one GPU, unsharded: {c4['default']['ms_per_frame']:.1f} (default), {c4['sharp_textured']['ms_per_frame']:.1f} (sharp textured) |")
-for g, (m, _) in multi.items():
+for g, (m, mname) in multi.items():
     if not m:
         continue
+    # a row from an older run set is scaled against THAT set's own 1-GPU line, and says so
+    tag = mname.split("_bench")[0]
+    note = ""
+    bv, be = base_v, base_e
+    if tag != one_name.split("_bench")[0]:
+        older = os.path.join(ROOT, "profiles", f"{tag}_bench.json")
+        if os.path.exists(older):
+            o = json.load(open(older))
+            bv, be = o["value"], o["e2e"]["value"]
+        note = f" [{tag}: measured before this round's last optimisations; × against {tag}'s own 1-GPU line]"
     cf = m["extra"]["configs"] or []
     ls = {}
     for c in cf:
         if "label_sharded" in c["workload"]:
             ls.setdefault(c["features"], []).append(f"{c['ms_per_frame']:.1f}" if "ms_per_frame" in c else "n/a")
     ip = [c for c in cf if "image_parallel" in c["workload"]]
-    print(f"| {g} | {m['value']:.0f} ({m['value'] / base_v:.2f}×) | {m['e2e']['value']:.0f} ({m['e2e']['value'] / base_e:.2f}×) | "
+    print(f"| {g}{note} | {m['value']:.0f} ({m['value'] / bv:.2f}×) | {m['e2e']['value']:.0f} ({m['e2e']['value'] / be:.2f}×) | "
           f"{ip[0]['value']:.1f} | default: {' / '.join(ls.get('default', []))}; sharp textured: {' / '.join(ls.get('sharp_textured', []))} |")
