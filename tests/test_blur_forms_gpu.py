@@ -99,7 +99,8 @@ def test_mean_field_loop_rotation_matches_barrier_form(native):
         scale = a.abs().max().item()
         noise = max((a - a2).abs().max().item(), (b - b2).abs().max().item())
         assert torch.isfinite(b).all()
-        assert (a - b).abs().max().item() <= max(4 * noise, 2e-5 * scale)
+        # same bound as the loop parity tests (2e-4 of the scale) unless the run-to-run spread is larger still
+        assert (a - b).abs().max().item() <= max(4 * noise, 2e-4 * scale)
         assert (a.argmin(1) == b.argmin(1)).float().mean().item() > 0.9995
     finally:
         lat.close()
