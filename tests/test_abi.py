@@ -53,3 +53,31 @@ def test_product_never_imports_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.replace("oracle/", "").lower() or f == "synthetic.py", \
                     os.path.join(dirpath, f)
+
+
+def test_transposed_compat_cache_tracks_identity_and_version():
+    """lattice._transposed(mu) (host logic, no device needed): one transposed copy per compatibility
+    tensor, invalidated by an in-place change, never matched by another tensor of the same address."""
+    import importlib
+    import torch
+    lat = importlib.import_module("depth_estimation_b200.lattice")
+    lat._MU_T.clear()
+    mu = torch.arange(12, dtype=torch.float32).reshape(3, 4)
+    t1 = lat._transposed(mu)
+    assert t1.shape == (4, 3) and t1.is_contiguous() and torch.equal(t1, mu.t())
+    assert lat._transposed(mu) is t1                       # remembered
+    mu.mul_(2.0)                                           # in-place change bumps the version counter
+    t2 = lat._transposed(mu)
+    assert t2 is not t1 and torch.equal(t2, mu.t())
+    other = mu.clone()
+    t3 = lat._transposed(other)
+    assert t3 is not t2 and torch.equal(t3, other.t())
+    # the cache keeps the tensors it has seen alive (so an id cannot be recycled) and stays small
+    for _ in range(3 * lat._MU_T_MAX):
+        lat._transposed(torch.rand(2, 2))
+    assert len(lat._MU_T) <= lat._MU_T_MAX
+    for key, (kept, _, _) in lat._MU_T.items():
+        assert id(kept) == key
+    # a tensor that requires grad is transposed detached
+    g = torch.rand(2, 3, requires_grad=True)
+    assert not lat._transposed(g).requires_grad
