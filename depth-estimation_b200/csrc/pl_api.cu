@@ -316,7 +316,8 @@ int pl_lattice_dim(const pl_lattice* lat) { return reinterpret_cast<const Lattic
 int64_t pl_lattice_num_vertices(const pl_lattice* lat) { return reinterpret_cast<const Lattice*>(lat)->M; }
 int64_t pl_lattice_device_bytes(const pl_lattice* lat) {
   const Lattice* L = reinterpret_cast<const Lattice*>(lat);
-  return L->bytes + 2 * (int64_t)sizeof(float) * L->ws_floats;
+  // the two value buffers, the rotating loop's third one and the barrier-free blur's 2 x 5 pass buffers
+  return L->bytes + (int64_t)sizeof(float) * ((L->val[2] != nullptr ? 3 : 2) * L->ws_floats + 10 * L->flow_floats);
 }
 
 int pl_lattice_apply(pl_lattice* lat, const float* src_dev, int64_t src_stride, float* dst_dev,
